@@ -1,0 +1,127 @@
+/*
+ * lt_b200.h — C ABI of the B200 (sm_100a) geometric hot path of learnable-triangulation.
+ *
+ * The reference (blufzzz/learnable-triangulation-pytorch) has no FFI layer: the hot path is three
+ * module-level Python functions. This header is the boundary a binding would bind instead of them:
+ *
+ *   lt_unproject_*   replaces  mvn/utils/op.py:99-163     unproject_heatmaps (+ multiview.py:80-101 projection)
+ *   lt_softargmax_*  replaces  mvn/utils/op.py:84-96      integrate_tensor_3d_with_coordinates
+ *   lt_dlt_*         replaces  mvn/utils/multiview.py:132-174  triangulate_batch_of_points /
+ *                                                              triangulate_point_from_multiple_views_linear_torch
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to contiguous fp32 (fp64 where the type says so) on the current
+ *     CUDA device; the library never allocates, never synchronises and never touches host memory;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - inputs are borrowed and never written; outputs are fully overwritten unless stated otherwise;
+ *   - return value: 0 on success, a cudaError_t (>0) if a launch failed, LT_ERR_INVALID (-1) for
+ *     bad arguments. lt_last_error() returns a thread-local message for the last non-zero return.
+ *     Nothing throws across this boundary.
+ *   - there is no CPU implementation behind any entry point.
+ */
+#ifndef LT_B200_H
+#define LT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LT_ABI_VERSION 1
+#define LT_ERR_INVALID (-1)
+
+/* view aggregation, op.py:147-161 (`conf` covers every method name starting with "conf") */
+enum lt_agg { LT_AGG_SUM = 0, LT_AGG_CONF = 1, LT_AGG_MAX = 2, LT_AGG_SOFTMAX = 3 };
+
+int lt_abi_version(void);
+const char *lt_last_error(void);
+
+/* ---- K0: feature layout ------------------------------------------------------------------------
+ * The reference hands (B,V,C,H,W) channel-planar maps to F.grid_sample (op.py:114-134). The gather
+ * kernels want one texel = one contiguous run of channels, so K0 re-tiles to (B·V,H,W,Cp), channels
+ * last, Cp = lt_padded_channels(C) >= C (zero filled). lt_feat_to_chw is the inverse, used for
+ * grad_heatmaps; it drops the padding. */
+int lt_padded_channels(int C);
+int lt_feat_to_hwc(const float *src_chw, float *dst_hwc, int BV, int C, int H, int W, void *stream);
+int lt_feat_to_chw(const float *src_hwc, float *dst_chw, int BV, int C, int H, int W, void *stream);
+
+/* ---- K1: fused unproject + view aggregation  (op.py:99-163) ------------------------------------
+ * feat_hwc (B,V,H,W,Cp)   proj (B,V,3,4)   coord (B,N0,N1,N2,3)   conf (B,V,C) or NULL
+ * out (B,C,N0,N1,N2).  align_corners: 0 = F.grid_sample default of torch>=1.3 (what the reference
+ * runs as today), 1 = torch 1.0.1 behaviour (requirements.txt:20).
+ * Semantics: p=[x y z 1]·Pᵀ; voxels with p.z<=0 contribute 0 for that view (op.py:121,138);
+ * gx=2(u/H-.5), gy=2(v/W-.5) (op.py:128-129, H for x and W for y as written); bilinear, zero padding;
+ * aggregation per enum lt_agg, zeroed views take part in max/softmax with value 0. */
+int lt_unproject_fwd(const float *feat_hwc, const float *proj, const float *coord, const float *conf,
+                     float *out, int B, int V, int C, int H, int W, int N0, int N1, int N2,
+                     int agg, int align_corners, void *stream);
+
+/* Backward of the above w.r.t. heatmaps and vol_confidences (proj/coord never need grad:
+ * triangulation.py:277,283). grad_feat_hwc (B,V,H,W,Cp) MUST be zero-filled by the caller: the
+ * kernel scatter-adds into it with vector reductions (non-deterministic summation order).
+ * grad_conf (B,V,C) may be NULL (required non-NULL only for LT_AGG_CONF if wanted); it is
+ * fully overwritten. conf_ws: scratch of lt_unproject_bwd_ws_bytes() bytes (may be NULL when
+ * grad_conf is NULL). */
+size_t lt_unproject_bwd_ws_bytes(int B, int V, int C, int N0, int N1, int N2);
+int lt_unproject_bwd(const float *grad_out, const float *feat_hwc, const float *proj,
+                     const float *coord, const float *conf, float *grad_feat_hwc, float *grad_conf,
+                     void *conf_ws, int B, int V, int C, int H, int W, int N0, int N1, int N2,
+                     int agg, int align_corners, void *stream);
+
+/* ---- K2: volumetric soft-argmax  (op.py:84-96) -------------------------------------------------
+ * vol (B,J,nvox) scaled by `multiplier` on the fly (triangulation.py:353 does volumes*multiplier
+ * before the call; pass 1.0 for the verbatim signature).  coord (B,nvox,3).
+ * softmax=1: prob=softmax over nvox; softmax=0: prob=relu(vol) un-normalised (op.py:91).
+ * coords (B,J,3) = sum_i prob_i * coord_i (op.py:94).  prob (B,J,nvox).
+ *
+ * The op is split where the z-slab sharded variant needs its one exchange:
+ *   partial : per (b,j) tuple stats[5] = {m, S=sum e^(x-m), sum e^(x-m)*xyz} over THIS buffer
+ *             (softmax=0: {0, 1, sum relu(x)*xyz}).  ws: lt_softargmax_ws_bytes() scratch.
+ *   (multi-GPU only: merge the tuples of all slabs — python does it with one all_gather)
+ *   finalize: prob_i = e^(x_i-m)/S and coords = stats[2:5]/S from (possibly merged) stats.
+ * lt_softargmax_fwd = partial + finalize on one device; stats (B,J,5) is kept for backward/debug. */
+size_t lt_softargmax_ws_bytes(int B, int J, long long nvox);
+int lt_softargmax_partial(const float *vol, const float *coord, float *stats, void *ws, int B, int J,
+                          long long nvox, int softmax, float multiplier, void *stream);
+int lt_softargmax_finalize(const float *vol, const float *stats, float *coords, float *prob, int B,
+                           int J, long long nvox, int softmax, float multiplier, void *stream);
+int lt_softargmax_fwd(const float *vol, const float *coord, float *coords, float *prob, float *stats,
+                      void *ws, int B, int J, long long nvox, int softmax, float multiplier,
+                      void *stream);
+/* log-sum-exp merge of R slabs' tuples: parts (R,B*J,5) -> merged (B*J,5); deterministic order. */
+int lt_softargmax_merge(const float *parts, float *merged, int R, int BJ, int softmax, void *stream);
+
+/* Backward.  grad_coords (B,J,3); grad_prob (B,J,nvox) or NULL (the dense gradient that arrives
+ * through the second return value, loss.py:76); prob = saved second output; coords = saved first
+ * output (global coordinates, also in the slab-sharded case); grad_vol (B,J,nvox) includes the
+ * `multiplier` factor.  softmax=1: g_i = p_i*(G_i - sum_k p_k G_k), G_i = gp_i + gc·xyz_i.
+ * dots (B,J) is only used when grad_prob != NULL: lt_softargmax_bwd_dot fills it with
+ * sum_k p_k*gp_k over THIS buffer (slab-sharded callers all-reduce it between the two calls). */
+int lt_softargmax_bwd_dot(const float *prob, const float *grad_prob, float *dots, void *ws, int B,
+                          int J, long long nvox, void *stream);
+int lt_softargmax_bwd(const float *prob, const float *coord, const float *coords,
+                      const float *grad_coords, const float *grad_prob, const float *dots,
+                      float *grad_vol, int B, int J, long long nvox, int softmax, float multiplier,
+                      void *stream);
+
+/* ---- K3: batched confidence-weighted DLT  (multiview.py:132-174) -------------------------------
+ * proj (B,V,3,4)  pts (B,V,J,2)  conf (B,V,J) or NULL (=> ones, multiview.py:147-148)
+ * out (B,J,3) fp32.  saved (B,J,LT_DLT_SAVED) fp64: right singular vectors + singular values of
+ * A (2V x 4), kept for backward.  Rows A[v,r,:] = conf_v*(pt[v,r]*P[v,2,:] - P[v,r,:]); the solve is
+ * a QR of A followed by a one-sided Jacobi SVD of the 4x4 R in fp64; X = h[:3]/h[3] with h the right
+ * singular vector of the smallest singular value. V <= LT_DLT_MAX_VIEWS. */
+#define LT_DLT_SAVED 20
+#define LT_DLT_MAX_VIEWS 64
+int lt_dlt_fwd(const float *proj, const float *pts, const float *conf, float *out, double *saved,
+               int B, int V, int J, void *stream);
+/* grad_pts (B,V,J,2), grad_conf (B,V,J) or NULL; fully overwritten. */
+int lt_dlt_bwd(const float *grad_out, const float *proj, const float *pts, const float *conf,
+               const double *saved, float *grad_pts, float *grad_conf, int B, int V, int J,
+               void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LT_B200_H */

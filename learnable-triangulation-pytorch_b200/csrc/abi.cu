@@ -1,0 +1,175 @@
+// abi.cu — the extern "C" surface declared in include/lt_b200.h. Argument checking, error strings and
+// dispatch only; every entry point ends in a kernel launch on the caller's stream (no CPU path exists).
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/lt_b200.h"
+#include "kernels.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail_invalid(const char* fn, const char* what) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", fn, what);
+  return LT_ERR_INVALID;
+}
+
+int finish(const char* fn, cudaError_t e) {
+  if (e == cudaSuccess) return 0;
+  snprintf(g_err, sizeof(g_err), "%s: CUDA error %d (%s)", fn, (int)e, cudaGetErrorString(e));
+  return (int)e;
+}
+
+inline cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
+
+bool bad_unproj_shape(int B, int V, int C, int H, int W, int N0, int N1, int N2) {
+  return B < 0 || V < 1 || C < 0 || H < 1 || W < 1 || N0 < 0 || N1 < 0 || N2 < 0 ||
+         (long long)H * W * lt::padded_channels(C > 0 ? C : 1) > 0x0fffffffLL;
+}
+
+}  // namespace
+
+#define LT_REQUIRE(cond, msg) \
+  do {                        \
+    if (!(cond)) return fail_invalid(__func__, msg); \
+  } while (0)
+
+#define LT_API __attribute__((visibility("default")))
+extern "C" {
+
+LT_API int lt_abi_version(void) { return LT_ABI_VERSION; }
+LT_API const char* lt_last_error(void) { return g_err; }
+
+LT_API int lt_padded_channels(int C) { return C > 0 ? lt::padded_channels(C) : 0; }
+
+LT_API int lt_feat_to_hwc(const float* src_chw, float* dst_hwc, int BV, int C, int H, int W, void* stream) {
+  LT_REQUIRE(BV >= 0 && C >= 0 && H >= 0 && W >= 0, "negative extent");
+  LT_REQUIRE(BV <= 65535, "B*V > 65535");
+  if ((long long)BV * C * H * W == 0) return 0;
+  LT_REQUIRE(src_chw && dst_hwc, "null pointer");
+  return finish(__func__, lt::launch_feat_layout(src_chw, dst_hwc, BV, C, H, W, true, as_stream(stream)));
+}
+
+LT_API int lt_feat_to_chw(const float* src_hwc, float* dst_chw, int BV, int C, int H, int W, void* stream) {
+  LT_REQUIRE(BV >= 0 && C >= 0 && H >= 0 && W >= 0, "negative extent");
+  LT_REQUIRE(BV <= 65535, "B*V > 65535");
+  if ((long long)BV * C * H * W == 0) return 0;
+  LT_REQUIRE(src_hwc && dst_chw, "null pointer");
+  return finish(__func__, lt::launch_feat_layout(src_hwc, dst_chw, BV, C, H, W, false, as_stream(stream)));
+}
+
+LT_API int lt_unproject_fwd(const float* feat_hwc, const float* proj, const float* coord, const float* conf, float* out,
+                     int B, int V, int C, int H, int W, int N0, int N1, int N2, int agg, int align_corners,
+                     void* stream) {
+  LT_REQUIRE(!bad_unproj_shape(B, V, C, H, W, N0, N1, N2), "bad shape");
+  LT_REQUIRE(agg >= LT_AGG_SUM && agg <= LT_AGG_SOFTMAX, "unknown aggregation");
+  if ((long long)B * C * N0 * N1 * N2 == 0) return 0;
+  LT_REQUIRE(feat_hwc && proj && coord && out, "null pointer");
+  LT_REQUIRE(agg != LT_AGG_CONF || conf, "conf aggregation needs vol_confidences");
+  lt::UnprojShape s{B, V, C, H, W, N0, N1, N2, agg, align_corners ? 1 : 0};
+  return finish(__func__, lt::launch_unproject_fwd(feat_hwc, proj, coord, conf, out, s, as_stream(stream)));
+}
+
+LT_API size_t lt_unproject_bwd_ws_bytes(int B, int V, int C, int N0, int N1, int N2) {
+  if (B <= 0 || V <= 0 || C <= 0) return 0;
+  return lt::unproject_bwd_ws_bytes(B, V, C, N0, N1, N2);
+}
+
+LT_API int lt_unproject_bwd(const float* grad_out, const float* feat_hwc, const float* proj, const float* coord,
+                     const float* conf, float* grad_feat_hwc, float* grad_conf, void* conf_ws, int B, int V, int C,
+                     int H, int W, int N0, int N1, int N2, int agg, int align_corners, void* stream) {
+  LT_REQUIRE(!bad_unproj_shape(B, V, C, H, W, N0, N1, N2), "bad shape");
+  LT_REQUIRE(agg >= LT_AGG_SUM && agg <= LT_AGG_SOFTMAX, "unknown aggregation");
+  if ((long long)B * C == 0) return 0;
+  LT_REQUIRE(feat_hwc && proj && coord && grad_feat_hwc, "null pointer");
+  LT_REQUIRE((long long)N0 * N1 * N2 == 0 || grad_out, "null grad_out");
+  LT_REQUIRE(agg != LT_AGG_CONF || conf, "conf aggregation needs vol_confidences");
+  LT_REQUIRE(!(agg == LT_AGG_CONF && grad_conf) || conf_ws, "grad_conf needs conf_ws");
+  lt::UnprojShape s{B, V, C, H, W, N0, N1, N2, agg, align_corners ? 1 : 0};
+  return finish(__func__, lt::launch_unproject_bwd(grad_out, feat_hwc, proj, coord, conf, grad_feat_hwc, grad_conf,
+                                                   conf_ws, s, as_stream(stream)));
+}
+
+LT_API size_t lt_softargmax_ws_bytes(int B, int J, long long nvox) {
+  if (B <= 0 || J <= 0 || nvox <= 0) return 0;
+  return lt::softargmax_ws_bytes(B, J, nvox);
+}
+
+LT_API int lt_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B, int J,
+                          long long nvox, int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0 && nvox >= 0, "negative extent");
+  LT_REQUIRE(B <= 65535, "B > 65535");
+  LT_REQUIRE(multiplier > 0.f, "multiplier must be > 0 (scale on the caller side otherwise)");
+  if (B * J == 0) return 0;
+  LT_REQUIRE(stats && (nvox == 0 || (vol && coord && ws)), "null pointer");
+  return finish(__func__, lt::launch_softargmax_partial(vol, coord, stats, ws, B, J, nvox, softmax ? 1 : 0,
+                                                        multiplier, as_stream(stream)));
+}
+
+LT_API int lt_softargmax_finalize(const float* vol, const float* stats, float* coords, float* prob, int B, int J,
+                           long long nvox, int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0 && nvox >= 0, "negative extent");
+  LT_REQUIRE((long long)B * J <= 65535, "B*J > 65535");
+  LT_REQUIRE(multiplier > 0.f, "multiplier must be > 0 (scale on the caller side otherwise)");
+  if (B * J == 0) return 0;
+  LT_REQUIRE(stats && (nvox == 0 || prob == nullptr || vol), "null pointer");
+  return finish(__func__, lt::launch_softargmax_finalize(vol, stats, coords, nvox == 0 ? nullptr : prob, B, J, nvox,
+                                                         softmax ? 1 : 0, multiplier, as_stream(stream)));
+}
+
+LT_API int lt_softargmax_fwd(const float* vol, const float* coord, float* coords, float* prob, float* stats, void* ws,
+                      int B, int J, long long nvox, int softmax, float multiplier, void* stream) {
+  int rc = lt_softargmax_partial(vol, coord, stats, ws, B, J, nvox, softmax, multiplier, stream);
+  if (rc) return rc;
+  return lt_softargmax_finalize(vol, stats, coords, prob, B, J, nvox, softmax, multiplier, stream);
+}
+
+LT_API int lt_softargmax_merge(const float* parts, float* merged, int R, int BJ, int softmax, void* stream) {
+  LT_REQUIRE(R >= 0 && BJ >= 0, "negative extent");
+  if (BJ == 0) return 0;
+  LT_REQUIRE(merged && (R == 0 || parts), "null pointer");
+  return finish(__func__, lt::launch_softargmax_merge(parts, merged, R, BJ, softmax ? 1 : 0, as_stream(stream)));
+}
+
+LT_API int lt_softargmax_bwd_dot(const float* prob, const float* grad_prob, float* dots, void* ws, int B, int J,
+                          long long nvox, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0 && nvox >= 0, "negative extent");
+  LT_REQUIRE((long long)B * J <= 65535, "B*J > 65535");
+  if (B * J == 0) return 0;
+  LT_REQUIRE(dots && (nvox == 0 || (prob && grad_prob && ws)), "null pointer");
+  return finish(__func__, lt::launch_softargmax_bwd_dot(prob, grad_prob, dots, ws, B, J, nvox, as_stream(stream)));
+}
+
+LT_API int lt_softargmax_bwd(const float* prob, const float* coord, const float* coords, const float* grad_coords,
+                      const float* grad_prob, const float* dots, float* grad_vol, int B, int J, long long nvox,
+                      int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0 && nvox >= 0, "negative extent");
+  LT_REQUIRE(B <= 65535, "B > 65535");
+  if ((long long)B * J * nvox == 0) return 0;
+  LT_REQUIRE(prob && coord && coords && grad_coords && grad_vol, "null pointer");
+  LT_REQUIRE(!(softmax && grad_prob) || dots, "grad_prob given without dots");
+  return finish(__func__, lt::launch_softargmax_bwd(prob, coord, coords, grad_coords, grad_prob, dots, grad_vol, B, J,
+                                                    nvox, softmax ? 1 : 0, multiplier, as_stream(stream)));
+}
+
+LT_API int lt_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out, double* saved, int B, int V,
+               int J, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0, "negative extent");
+  LT_REQUIRE(V >= 1 && V <= LT_DLT_MAX_VIEWS, "need 1 <= V <= LT_DLT_MAX_VIEWS");
+  if (B * J == 0) return 0;
+  LT_REQUIRE(proj && pts && out, "null pointer");
+  return finish(__func__, lt::launch_dlt_fwd(proj, pts, conf, out, saved, B, V, J, as_stream(stream)));
+}
+
+LT_API int lt_dlt_bwd(const float* grad_out, const float* proj, const float* pts, const float* conf, const double* saved,
+               float* grad_pts, float* grad_conf, int B, int V, int J, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0, "negative extent");
+  LT_REQUIRE(V >= 1 && V <= LT_DLT_MAX_VIEWS, "need 1 <= V <= LT_DLT_MAX_VIEWS");
+  if (B * J == 0) return 0;
+  LT_REQUIRE(grad_out && proj && pts && saved && grad_pts, "null pointer");
+  return finish(__func__, lt::launch_dlt_bwd(grad_out, proj, pts, conf, saved, grad_pts, grad_conf, B, V, J,
+                                             as_stream(stream)));
+}
+
+}  // extern "C"

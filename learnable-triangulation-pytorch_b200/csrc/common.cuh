@@ -1,0 +1,99 @@
+// common.cuh — shared device helpers for the lt_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "lt_b200 kernels are written for sm_100a (B200) only"
+#endif
+
+namespace lt {
+
+constexpr int kWarp = 32;
+
+// ---- 256-bit global accesses (LDG.E.256 / STG.E.256, new on sm_100) and vector reductions --------
+struct alignas(32) f8 { float v[8]; };
+
+__device__ __forceinline__ f8 ldg256_nc(const float* p) {
+  f8 r;
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]),
+                 "=f"(r.v[6]), "=f"(r.v[7])
+               : "l"(p));
+  return r;
+}
+// streaming variant: data read exactly once (upstream gradients), keep it out of L1
+__device__ __forceinline__ f8 ldg256_stream(const float* p) {
+  f8 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]),
+                 "=f"(r.v[6]), "=f"(r.v[7])
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg256(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]),
+               "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+               : "memory");
+}
+__device__ __forceinline__ float4 ldg128_nc(const float* p) {
+  return __ldg(reinterpret_cast<const float4*>(p));
+}
+__device__ __forceinline__ float4 ldg128_stream(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg128_stream(float* p, float4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+// REDG.E.ADD.F32x4: one 16-byte fire-and-forget reduction at L2 (sm_90+)
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+// ---- warp / block reductions ----------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// online-softmax tuple (m, s, wx, wy, wz): s = sum e^(x-m), w = sum e^(x-m) * xyz
+struct Lse5 {
+  float m, s, x, y, z;
+};
+__device__ __forceinline__ Lse5 lse_identity() { return {-INFINITY, 0.f, 0.f, 0.f, 0.f}; }
+__device__ __forceinline__ Lse5 lse_merge(const Lse5& a, const Lse5& b) {
+  float m = fmaxf(a.m, b.m);
+  if (m == -INFINITY) return lse_identity();
+  float fa = expf(a.m - m), fb = expf(b.m - m);
+  return {m, a.s * fa + b.s * fb, a.x * fa + b.x * fb, a.y * fa + b.y * fb, a.z * fa + b.z * fb};
+}
+__device__ __forceinline__ Lse5 lse_shfl_xor(const Lse5& a, int o) {
+  return {__shfl_xor_sync(0xffffffffu, a.m, o), __shfl_xor_sync(0xffffffffu, a.s, o),
+          __shfl_xor_sync(0xffffffffu, a.x, o), __shfl_xor_sync(0xffffffffu, a.y, o),
+          __shfl_xor_sync(0xffffffffu, a.z, o)};
+}
+__device__ __forceinline__ Lse5 lse_warp_reduce(Lse5 a) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a = lse_merge(a, lse_shfl_xor(a, o));
+  return a;
+}
+
+}  // namespace lt

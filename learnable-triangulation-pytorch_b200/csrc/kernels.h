@@ -1,0 +1,45 @@
+// kernels.h — internal C++ launch interface between abi.cu and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+namespace lt {
+
+constexpr int kAggSum = 0, kAggConf = 1, kAggMax = 2, kAggSoftmax = 3;  // == enum lt_agg
+
+int padded_channels(int C);
+cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwc,
+                               cudaStream_t st);
+
+struct UnprojShape {
+  int B, V, C, H, W, N0, N1, N2, agg, align_corners;
+};
+cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const float* coord,
+                                 const float* conf, float* out, const UnprojShape& s, cudaStream_t st);
+size_t unproject_bwd_ws_bytes(int B, int V, int C, int N0, int N1, int N2);
+cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, const float* proj,
+                                 const float* coord, const float* conf, float* grad_feat_hwc,
+                                 float* grad_conf, void* conf_ws, const UnprojShape& s, cudaStream_t st);
+
+size_t softargmax_ws_bytes(int B, int J, long long nvox);
+cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,
+                                      int J, long long nvox, int softmax, float mult, cudaStream_t st);
+cudaError_t launch_softargmax_finalize(const float* vol, const float* stats, float* coords, float* prob,
+                                       int B, int J, long long nvox, int softmax, float mult,
+                                       cudaStream_t st);
+cudaError_t launch_softargmax_merge(const float* parts, float* merged, int R, int BJ, int softmax,
+                                    cudaStream_t st);
+cudaError_t launch_softargmax_bwd_dot(const float* prob, const float* grad_prob, float* dots, void* ws,
+                                      int B, int J, long long nvox, cudaStream_t st);
+cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const float* coords,
+                                  const float* grad_coords, const float* grad_prob, const float* dots,
+                                  float* grad_vol, int B, int J, long long nvox, int softmax, float mult,
+                                  cudaStream_t st);
+
+cudaError_t launch_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out,
+                           double* saved, int B, int V, int J, cudaStream_t st);
+cudaError_t launch_dlt_bwd(const float* grad_out, const float* proj, const float* pts, const float* conf,
+                           const double* saved, float* grad_pts, float* grad_conf, int B, int V, int J,
+                           cudaStream_t st);
+
+}  // namespace lt

@@ -1,0 +1,414 @@
+// softargmax.cu — K2: volumetric soft-argmax in world coordinates, forward and backward.
+//
+// Replaces mvn/utils/op.py:84-96: softmax over each joint's flattened volume (or relu, un-normalised),
+// then einsum("bnxyz,bxyzc->bnc") with the coordinate volume. Both outputs are produced: coordinates
+// (B,J,3) and the normalised volume (B,J,nvox) that VolumetricCELoss indexes (mvn/models/loss.py:76).
+//
+// Structure (also the multi-GPU z-slab structure): the op is split where the one exchange
+// of the sharded variant sits.
+//   k_sam_stats   : grid (chunk, b). A CTA owns a chunk of voxels, keeps their xyz in registers and walks
+//                   all J joints over them (coordinates are fetched once per voxel, not once per joint).
+//                   Per (joint, warp) it emits one online-softmax tuple (m, S, Sx, Sy, Sz).
+//   k_sam_combine : one warp per (b, joint) merges the tuples (fixed order => deterministic).
+//   k_sam_final   : prob = e^(x-m)/S, streaming; coords = (Sx,Sy,Sz)/S.
+// exp is evaluated as ex2(fma(x, mult*log2e, -m*log2e)): one FFMA + one MUFU per element; the shift is
+// common to numerator and denominator so only the rounding of log2e (3e-8 * |x-m|) enters the result.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace lt {
+
+constexpr int kSamThreads = 256;
+constexpr int kSamEpt = 16;                          // voxels per thread: 4 groups of 4 (float4)
+constexpr int kSamChunk = kSamThreads * kSamEpt;     // 4096 voxels per CTA
+constexpr int kSamWarps = kSamThreads / 32;
+constexpr float kLog2e = 1.4426950408889634f;
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+static inline int sam_chunks(long long nvox) { return (int)((nvox + kSamChunk - 1) / kSamChunk); }
+
+// ---------------------------------------------------------------------------------------------------
+// pass 1: partial tuples. ws layout: [(b*J + j)][chunk*kSamWarps + warp][5]
+// VEC: nvox % 4 == 0 (rows 16-byte aligned) -> 128-bit loads.
+template <bool VEC, bool SOFTMAX>
+__global__ void __launch_bounds__(kSamThreads) k_sam_stats(const float* __restrict__ vol,
+                                                           const float* __restrict__ coord,
+                                                           float* __restrict__ ws, int J, long long nvox,
+                                                           float mult) {
+  const int b = blockIdx.y, chunk = blockIdx.x, nchunk = gridDim.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long base = (long long)chunk * kSamChunk;
+  const float* cb = coord + (size_t)b * nvox * 3;
+
+  // coordinates of this thread's 16 voxels: group i covers voxels base + (i*256 + tid)*4 .. +3
+  float cx[kSamEpt], cy[kSamEpt], cz[kSamEpt];
+  bool ok[kSamEpt / 4];
+#pragma unroll
+  for (int i = 0; i < kSamEpt / 4; ++i) {
+    const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+    ok[i] = VEC ? (v0 < nvox) : (v0 + 3 < nvox);
+    if (ok[i]) {
+      const float4* p = reinterpret_cast<const float4*>(cb + v0 * 3);
+      float4 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
+      cx[i * 4 + 0] = a.x;  cy[i * 4 + 0] = a.y;  cz[i * 4 + 0] = a.z;
+      cx[i * 4 + 1] = a.w;  cy[i * 4 + 1] = bb.x; cz[i * 4 + 1] = bb.y;
+      cx[i * 4 + 2] = bb.z; cy[i * 4 + 2] = bb.w; cz[i * 4 + 2] = c.x;
+      cx[i * 4 + 3] = c.y;  cy[i * 4 + 3] = c.z;  cz[i * 4 + 3] = c.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const long long v = v0 + e;
+        const bool in = v < nvox;
+        cx[i * 4 + e] = in ? __ldg(cb + v * 3) : 0.f;
+        cy[i * 4 + e] = in ? __ldg(cb + v * 3 + 1) : 0.f;
+        cz[i * 4 + e] = in ? __ldg(cb + v * 3 + 2) : 0.f;
+      }
+    }
+  }
+
+  const float L = mult * kLog2e;
+  for (int j = 0; j < J; ++j) {
+    const float* row = vol + ((size_t)b * J + j) * nvox;
+    float x[kSamEpt];
+#pragma unroll
+    for (int i = 0; i < kSamEpt / 4; ++i) {
+      const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+      if (VEC && ok[i]) {
+        float4 t = ldg128_stream(row + v0);
+        x[i * 4] = t.x; x[i * 4 + 1] = t.y; x[i * 4 + 2] = t.z; x[i * 4 + 3] = t.w;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) x[i * 4 + e] = (v0 + e < nvox) ? __ldg(row + v0 + e) : -INFINITY;
+      }
+    }
+    Lse5 r;
+    if (SOFTMAX) {
+      // shift by the warp-wide max of the scaled logits (mult > 0 is guaranteed by the caller); padding
+      // voxels carry -inf and contribute e = 0.
+      float ms = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < kSamEpt; ++i) ms = fmaxf(ms, x[i] * mult);
+      const float wm = warp_max(ms);  // warp-wide shift: one rescale-free accumulation per warp
+      float s = 0.f, sx = 0.f, sy = 0.f, sz = 0.f;
+      if (wm > -INFINITY) {
+        const float shift = -wm * kLog2e;
+#pragma unroll
+        for (int i = 0; i < kSamEpt; ++i) {
+          const float e = (x[i] == -INFINITY) ? 0.f : ex2_approx(fmaf(x[i], L, shift));
+          s += e;
+          sx = fmaf(e, cx[i], sx);
+          sy = fmaf(e, cy[i], sy);
+          sz = fmaf(e, cz[i], sz);
+        }
+      }
+      r = {wm, warp_sum(s), warp_sum(sx), warp_sum(sy), warp_sum(sz)};
+    } else {
+      float sx = 0.f, sy = 0.f, sz = 0.f;
+#pragma unroll
+      for (int i = 0; i < kSamEpt; ++i) {
+        const float e = (x[i] == -INFINITY) ? 0.f : fmaxf(x[i] * mult, 0.f);
+        sx = fmaf(e, cx[i], sx);
+        sy = fmaf(e, cy[i], sy);
+        sz = fmaf(e, cz[i], sz);
+      }
+      r = {0.f, 1.f, warp_sum(sx), warp_sum(sy), warp_sum(sz)};
+    }
+    if (lane == 0) {
+      float* o = ws + (((size_t)b * J + j) * nchunk * kSamWarps + (size_t)chunk * kSamWarps + warp) * 5;
+      o[0] = r.m; o[1] = r.s; o[2] = r.x; o[3] = r.y; o[4] = r.z;
+    }
+  }
+}
+
+// merge P tuples per (b,j): one warp each, lanes stride over the tuples, then a fixed butterfly.
+template <bool SOFTMAX>
+__global__ void k_sam_combine(const float* __restrict__ parts, float* __restrict__ stats, int P, int BJ,
+                              size_t part_stride /* floats between consecutive (b,j) */,
+                              size_t tuple_stride /* floats between consecutive tuples of one (b,j) */) {
+  const int bj = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (bj >= BJ) return;
+  const float* p = parts + (size_t)bj * part_stride;
+  Lse5 acc = SOFTMAX ? lse_identity() : Lse5{0.f, 1.f, 0.f, 0.f, 0.f};
+  if (SOFTMAX) {
+    for (int i = lane; i < P; i += 32) {
+      const float* t = p + (size_t)i * tuple_stride;
+      acc = lse_merge(acc, Lse5{t[0], t[1], t[2], t[3], t[4]});
+    }
+    acc = lse_warp_reduce(acc);
+  } else {
+    float x = 0.f, y = 0.f, z = 0.f;
+    for (int i = lane; i < P; i += 32) {
+      const float* t = p + (size_t)i * tuple_stride;
+      x += t[2]; y += t[3]; z += t[4];
+    }
+    acc = {0.f, 1.f, warp_sum(x), warp_sum(y), warp_sum(z)};
+  }
+  if (lane == 0) {
+    float* o = stats + (size_t)bj * 5;
+    o[0] = acc.m; o[1] = acc.s; o[2] = acc.x; o[3] = acc.y; o[4] = acc.z;
+  }
+}
+
+// pass 2: prob = e^(mult*x - m)/S (softmax) or relu(mult*x); coords = (Sx,Sy,Sz)/S.
+template <bool VEC, bool SOFTMAX>
+__global__ void __launch_bounds__(kSamThreads) k_sam_final(const float* __restrict__ vol,
+                                                           const float* __restrict__ stats,
+                                                           float* __restrict__ coords, float* __restrict__ prob,
+                                                           long long nvox, float mult) {
+  const int bj = blockIdx.y, chunk = blockIdx.x;
+  const float* st = stats + (size_t)bj * 5;
+  const float m = __ldg(st), S = __ldg(st + 1);
+  const float invS = SOFTMAX ? __fdiv_rn(1.f, S) : 1.f;
+  if (chunk == 0 && threadIdx.x < 3 && coords != nullptr)
+    coords[(size_t)bj * 3 + threadIdx.x] = SOFTMAX ? __fdiv_rn(__ldg(st + 2 + threadIdx.x), S) : __ldg(st + 2 + threadIdx.x);
+  if (prob == nullptr) return;
+  const float L = mult * kLog2e, shift = -m * kLog2e;
+  const float* row = vol + (size_t)bj * nvox;
+  float* orow = prob + (size_t)bj * nvox;
+  const long long base = (long long)chunk * kSamChunk;
+#pragma unroll
+  for (int i = 0; i < kSamEpt / 4; ++i) {
+    const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+    if (VEC) {
+      if (v0 < nvox) {
+        float4 t = ldg128_stream(row + v0), o;
+        if (SOFTMAX) {
+          o.x = ex2_approx(fmaf(t.x, L, shift)) * invS; o.y = ex2_approx(fmaf(t.y, L, shift)) * invS;
+          o.z = ex2_approx(fmaf(t.z, L, shift)) * invS; o.w = ex2_approx(fmaf(t.w, L, shift)) * invS;
+        } else {
+          o.x = fmaxf(t.x * mult, 0.f); o.y = fmaxf(t.y * mult, 0.f);
+          o.z = fmaxf(t.z * mult, 0.f); o.w = fmaxf(t.w * mult, 0.f);
+        }
+        stg128_stream(orow + v0, o);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (v0 + e < nvox) {
+          const float t = __ldg(row + v0 + e);
+          orow[v0 + e] = SOFTMAX ? ex2_approx(fmaf(t, L, shift)) * invS : fmaxf(t * mult, 0.f);
+        }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// backward
+//   softmax: g_i = mult * p_i * (gp_i + gc.xyz_i - dot),  dot = sum_k p_k gp_k + gc.coords
+//   relu   : g_i = mult * [p_i > 0] * (gp_i + gc.xyz_i)
+// grid (chunk, b): coordinates in registers, loop over joints (same reuse as k_sam_stats).
+template <bool VEC, bool SOFTMAX, bool HAS_GP>
+__global__ void __launch_bounds__(kSamThreads) k_sam_bwd(const float* __restrict__ prob,
+                                                         const float* __restrict__ coord,
+                                                         const float* __restrict__ coords_out,
+                                                         const float* __restrict__ gcoords,
+                                                         const float* __restrict__ gprob,
+                                                         const float* __restrict__ dots, float* __restrict__ gvol,
+                                                         int J, long long nvox, float mult) {
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const long long base = (long long)chunk * kSamChunk;
+  const float* cb = coord + (size_t)b * nvox * 3;
+  float cx[kSamEpt], cy[kSamEpt], cz[kSamEpt];
+#pragma unroll
+  for (int i = 0; i < kSamEpt / 4; ++i) {
+    const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+    if (VEC && v0 < nvox) {
+      const float4* p = reinterpret_cast<const float4*>(cb + v0 * 3);
+      float4 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
+      cx[i * 4 + 0] = a.x;  cy[i * 4 + 0] = a.y;  cz[i * 4 + 0] = a.z;
+      cx[i * 4 + 1] = a.w;  cy[i * 4 + 1] = bb.x; cz[i * 4 + 1] = bb.y;
+      cx[i * 4 + 2] = bb.z; cy[i * 4 + 2] = bb.w; cz[i * 4 + 2] = c.x;
+      cx[i * 4 + 3] = c.y;  cy[i * 4 + 3] = c.z;  cz[i * 4 + 3] = c.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const long long v = v0 + e;
+        const bool in = v < nvox;
+        cx[i * 4 + e] = in ? __ldg(cb + v * 3) : 0.f;
+        cy[i * 4 + e] = in ? __ldg(cb + v * 3 + 1) : 0.f;
+        cz[i * 4 + e] = in ? __ldg(cb + v * 3 + 2) : 0.f;
+      }
+    }
+  }
+  for (int j = 0; j < J; ++j) {
+    const size_t bj = (size_t)b * J + j;
+    const float gx = __ldg(gcoords + bj * 3), gy = __ldg(gcoords + bj * 3 + 1), gz = __ldg(gcoords + bj * 3 + 2);
+    float dot = 0.f;
+    if (SOFTMAX) {
+      dot = gx * __ldg(coords_out + bj * 3) + gy * __ldg(coords_out + bj * 3 + 1) + gz * __ldg(coords_out + bj * 3 + 2);
+      if (HAS_GP) dot += __ldg(dots + bj);
+    }
+    const float* prow = prob + bj * nvox;
+    const float* grow = HAS_GP ? gprob + bj * nvox : nullptr;
+    float* orow = gvol + bj * nvox;
+#pragma unroll
+    for (int i = 0; i < kSamEpt / 4; ++i) {
+      const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+      float p[4], gp[4] = {0.f, 0.f, 0.f, 0.f}, o[4];
+      if (VEC) {
+        if (v0 >= nvox) continue;
+        float4 t = ldg128_stream(prow + v0);
+        p[0] = t.x; p[1] = t.y; p[2] = t.z; p[3] = t.w;
+        if (HAS_GP) {
+          float4 u = ldg128_stream(grow + v0);
+          gp[0] = u.x; gp[1] = u.y; gp[2] = u.z; gp[3] = u.w;
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          p[e] = (v0 + e < nvox) ? __ldg(prow + v0 + e) : 0.f;
+          if (HAS_GP) gp[e] = (v0 + e < nvox) ? __ldg(grow + v0 + e) : 0.f;
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float G = gp[e] + (gx * cx[i * 4 + e] + gy * cy[i * 4 + e] + gz * cz[i * 4 + e]);
+        if (SOFTMAX) o[e] = mult * (p[e] * (G - dot));
+        else o[e] = (p[e] > 0.f) ? mult * G : 0.f;
+      }
+      if (VEC) {
+        stg128_stream(orow + v0, make_float4(o[0], o[1], o[2], o[3]));
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (v0 + e < nvox) orow[v0 + e] = o[e];
+      }
+    }
+  }
+}
+
+// partial sums of p*gp: ws[(bj)][chunk*kSamWarps + warp]
+template <bool VEC>
+__global__ void __launch_bounds__(kSamThreads) k_sam_dot(const float* __restrict__ prob,
+                                                         const float* __restrict__ gprob, float* __restrict__ ws,
+                                                         long long nvox) {
+  const int bj = blockIdx.y, chunk = blockIdx.x, nchunk = gridDim.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float* prow = prob + (size_t)bj * nvox;
+  const float* grow = gprob + (size_t)bj * nvox;
+  const long long base = (long long)chunk * kSamChunk;
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kSamEpt / 4; ++i) {
+    const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+    if (VEC) {
+      if (v0 < nvox) {
+        float4 a = ldg128_nc(prow + v0), g = ldg128_nc(grow + v0);
+        s = fmaf(a.x, g.x, s); s = fmaf(a.y, g.y, s); s = fmaf(a.z, g.z, s); s = fmaf(a.w, g.w, s);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (v0 + e < nvox) s = fmaf(__ldg(prow + v0 + e), __ldg(grow + v0 + e), s);
+    }
+  }
+  s = warp_sum(s);
+  if (lane == 0) ws[(size_t)bj * nchunk * kSamWarps + (size_t)chunk * kSamWarps + warp] = s;
+}
+
+__global__ void k_sam_dot_combine(const float* __restrict__ ws, float* __restrict__ dots, int P, int BJ) {
+  const int bj = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (bj >= BJ) return;
+  float s = 0.f;
+  for (int i = lane; i < P; i += 32) s += ws[(size_t)bj * P + i];
+  s = warp_sum(s);
+  if (lane == 0) dots[bj] = s;
+}
+
+// ---------------------------------------------------------------------------------------------------
+size_t softargmax_ws_bytes(int B, int J, long long nvox) {
+  return (size_t)B * J * sam_chunks(nvox) * kSamWarps * 5 * sizeof(float);
+}
+
+cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,
+                                      int J, long long nvox, int softmax, float mult, cudaStream_t st) {
+  if (B * J == 0) return cudaSuccess;
+  if (nvox == 0) {  // empty volume: identity tuples
+    return launch_softargmax_merge(nullptr, stats, 0, B * J, softmax, st);
+  }
+  const int nchunk = sam_chunks(nvox);
+  const bool vec = (nvox % 4) == 0;
+  dim3 grid(nchunk, B);
+  float* w = static_cast<float*>(ws);
+#define LT_GO(V_, S_) k_sam_stats<V_, S_><<<grid, kSamThreads, 0, st>>>(vol, coord, w, J, nvox, mult)
+  if (vec) { if (softmax) LT_GO(true, true); else LT_GO(true, false); }
+  else     { if (softmax) LT_GO(false, true); else LT_GO(false, false); }
+#undef LT_GO
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const int P = nchunk * kSamWarps, BJ = B * J;
+  const int wpb = 4;
+  if (softmax) k_sam_combine<true><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
+  else k_sam_combine<false><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_softargmax_merge(const float* parts, float* merged, int R, int BJ, int softmax,
+                                    cudaStream_t st) {
+  if (BJ == 0) return cudaSuccess;
+  const int wpb = 4;
+  // parts (R, BJ, 5): tuples of one (b,j) are BJ*5 floats apart
+  if (softmax) k_sam_combine<true><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(parts, merged, R, BJ, 5, (size_t)BJ * 5);
+  else k_sam_combine<false><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(parts, merged, R, BJ, 5, (size_t)BJ * 5);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_softargmax_finalize(const float* vol, const float* stats, float* coords, float* prob,
+                                       int B, int J, long long nvox, int softmax, float mult,
+                                       cudaStream_t st) {
+  if (B * J == 0) return cudaSuccess;
+  const int nchunk = nvox == 0 ? 1 : sam_chunks(nvox);
+  const bool vec = (nvox % 4) == 0;
+  dim3 grid(nchunk, B * J);
+#define LT_GO(V_, S_) k_sam_final<V_, S_><<<grid, kSamThreads, 0, st>>>(vol, stats, coords, prob, nvox, mult)
+  if (vec) { if (softmax) LT_GO(true, true); else LT_GO(true, false); }
+  else     { if (softmax) LT_GO(false, true); else LT_GO(false, false); }
+#undef LT_GO
+  return cudaGetLastError();
+}
+
+cudaError_t launch_softargmax_bwd_dot(const float* prob, const float* grad_prob, float* dots, void* ws,
+                                      int B, int J, long long nvox, cudaStream_t st) {
+  const int BJ = B * J;
+  if (BJ == 0) return cudaSuccess;
+  if (nvox == 0) return cudaMemsetAsync(dots, 0, (size_t)BJ * sizeof(float), st);
+  const int nchunk = sam_chunks(nvox);
+  dim3 grid(nchunk, BJ);
+  float* w = static_cast<float*>(ws);
+  if (nvox % 4 == 0) k_sam_dot<true><<<grid, kSamThreads, 0, st>>>(prob, grad_prob, w, nvox);
+  else k_sam_dot<false><<<grid, kSamThreads, 0, st>>>(prob, grad_prob, w, nvox);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const int wpb = 4;
+  k_sam_dot_combine<<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(w, dots, nchunk * kSamWarps, BJ);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const float* coords,
+                                  const float* grad_coords, const float* grad_prob, const float* dots,
+                                  float* grad_vol, int B, int J, long long nvox, int softmax, float mult,
+                                  cudaStream_t st) {
+  if (B * J == 0 || nvox == 0) return cudaSuccess;
+  dim3 grid(sam_chunks(nvox), B);
+  const bool vec = (nvox % 4) == 0, gp = grad_prob != nullptr;
+#define LT_GO(V_, S_, G_) \
+  k_sam_bwd<V_, S_, G_><<<grid, kSamThreads, 0, st>>>(prob, coord, coords, grad_coords, grad_prob, dots, grad_vol, J, nvox, mult)
+  if (vec) {
+    if (softmax) { if (gp) LT_GO(true, true, true); else LT_GO(true, true, false); }
+    else         { if (gp) LT_GO(true, false, true); else LT_GO(true, false, false); }
+  } else {
+    if (softmax) { if (gp) LT_GO(false, true, true); else LT_GO(false, true, false); }
+    else         { if (gp) LT_GO(false, false, true); else LT_GO(false, false, false); }
+  }
+#undef LT_GO
+  return cudaGetLastError();
+}
+
+}  // namespace lt

@@ -1,0 +1,205 @@
+"""Drop-in replacements for the two volumetric functions of ``mvn.utils.op`` (reference file
+``mvn/utils/op.py``): same names, same positional/keyword arguments, same return values, same exceptions.
+Everything runs in hand-written sm_100a kernels behind the C ABI of ``include/lt_b200.h``; there is no CPU path.
+
+    unproject_heatmaps(heatmaps, proj_matricies, coord_volumes, volume_aggregation_method='sum', vol_confidences=None)
+        reference: mvn/utils/op.py:99-163
+    integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True)
+        reference: mvn/utils/op.py:84-96
+"""
+import torch
+
+from . import _lib
+
+_AGG = {"sum": 0, "max": 2, "softmax": 3}  # 'conf*' -> 1, see _agg_code
+
+
+def _agg_code(method):
+    # op.py:147-161: startswith('conf') first, then exact names, else ValueError with this exact text
+    if method.startswith("conf"):
+        return 1
+    if method in _AGG:
+        return _AGG[method]
+    raise ValueError("Unknown volume_aggregation_method: {}".format(method))
+
+
+def _require_cuda(name, t):
+    if not torch.is_tensor(t):
+        raise TypeError("{} must be a torch tensor".format(name))
+    if not t.is_cuda:
+        raise RuntimeError(
+            "lt_b200: {} is on {}; these ops only exist as CUDA kernels (no CPU fallback)".format(name, t.device))
+
+
+def _f32c(t):
+    return t.detach().to(torch.float32).contiguous()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class _Unproject(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, heatmaps, proj, coord, conf, agg, align_corners):
+        L = _lib.lib()
+        B, V, C, H, W = heatmaps.shape
+        N0, N1, N2 = coord.shape[1:4]
+        Cp = L.lt_padded_channels(C) if C > 0 else 0
+        with torch.cuda.device(heatmaps.device):
+            st = _stream()
+            hm = _f32c(heatmaps)
+            proj_c, coord_c = _f32c(proj), _f32c(coord)
+            conf_c = _f32c(conf) if conf is not None else None
+            # K0: channels-last, padded copy of the feature maps (one texel = one contiguous run)
+            feat = torch.empty((B, V, H, W, Cp), device=hm.device, dtype=torch.float32)
+            _lib.check(L.lt_feat_to_hwc(_lib.ptr(hm), _lib.ptr(feat), B * V, C, H, W, st))
+            out = torch.empty((B, C, N0, N1, N2), device=hm.device, dtype=torch.float32)
+            _lib.check(L.lt_unproject_fwd(_lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c), _lib.ptr(conf_c),
+                                          _lib.ptr(out), B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
+        ctx.save_for_backward(feat, proj_c, coord_c, conf_c)
+        ctx.meta = (B, V, C, H, W, N0, N1, N2, agg, align_corners, heatmaps.dtype,
+                    conf.dtype if conf is not None else None)
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, grad_out):
+        L = _lib.lib()
+        feat, proj_c, coord_c, conf_c = ctx.saved_tensors
+        B, V, C, H, W, N0, N1, N2, agg, align_corners, hm_dtype, conf_dtype = ctx.meta
+        need_hm, need_conf = ctx.needs_input_grad[0], ctx.needs_input_grad[3] and conf_c is not None
+        g_hm = g_conf = None
+        if not (need_hm or need_conf):
+            return None, None, None, None, None, None
+        with torch.cuda.device(feat.device):
+            st = _stream()
+            go = _f32c(grad_out)
+            gfeat = torch.zeros_like(feat)  # the kernel scatter-adds into it
+            gconf = ws = None
+            if need_conf:
+                gconf = torch.empty((B, V, C), device=feat.device, dtype=torch.float32)
+                nbytes = L.lt_unproject_bwd_ws_bytes(B, V, C, N0, N1, N2)
+                ws = torch.empty((max(nbytes, 4) // 4,), device=feat.device, dtype=torch.float32)
+            _lib.check(L.lt_unproject_bwd(_lib.ptr(go), _lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c),
+                                          _lib.ptr(conf_c), _lib.ptr(gfeat), _lib.ptr(gconf), _lib.ptr(ws),
+                                          B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
+            if need_hm:
+                g_hm = torch.empty((B, V, C, H, W), device=feat.device, dtype=torch.float32)
+                _lib.check(L.lt_feat_to_chw(_lib.ptr(gfeat), _lib.ptr(g_hm), B * V, C, H, W, st))
+                g_hm = g_hm.to(hm_dtype)
+            if need_conf:
+                g_conf = gconf.to(conf_dtype)
+        return g_hm, None, None, g_conf, None, None
+
+
+def unproject_heatmaps(heatmaps, proj_matricies, coord_volumes, volume_aggregation_method='sum',
+                       vol_confidences=None, *, align_corners=None):
+    """Lift V feature maps per batch item into one aggregated 3-D volume (reference: op.py:99-163).
+
+    heatmaps (B,V,C,H,W), proj_matricies (B,V,3,4), coord_volumes (B,N0,N1,N2,3), vol_confidences (B,V,C) or None.
+    Returns (B,C,N0,N1,N2) float32, always (the reference allocates its output with the default dtype, op.py:104).
+    ``align_corners`` (keyword only): None/False = what ``F.grid_sample`` does by default on torch >= 1.3, i.e. what
+    the reference computes today; True = the behaviour under its pinned torch 1.0.1.
+    Differentiable w.r.t. heatmaps and vol_confidences.
+    """
+    agg = _agg_code(volume_aggregation_method)
+    if agg == 1 and vol_confidences is None:
+        # the reference fails on `vol_confidences[batch_i]` (op.py:148)
+        raise TypeError("'NoneType' object is not subscriptable")
+    _require_cuda("heatmaps", heatmaps)
+    _require_cuda("proj_matricies", proj_matricies)
+    _require_cuda("coord_volumes", coord_volumes)
+    if heatmaps.dim() != 5:
+        raise RuntimeError("heatmaps must be (B,V,C,H,W), got {}".format(tuple(heatmaps.shape)))
+    B, V = heatmaps.shape[:2]
+    if coord_volumes.dim() != 5 or coord_volumes.shape[-1] != 3 or coord_volumes.shape[0] < B:
+        raise RuntimeError("coord_volumes must be (B,N0,N1,N2,3), got {}".format(tuple(coord_volumes.shape)))
+    if tuple(proj_matricies.shape[-2:]) != (3, 4) or proj_matricies.shape[0] < B or proj_matricies.shape[1] < V:
+        raise RuntimeError("proj_matricies must be (B,V,3,4), got {}".format(tuple(proj_matricies.shape)))
+    if V == 0:
+        raise RuntimeError("unproject_heatmaps needs at least one view")
+    conf = None
+    if agg == 1:
+        _require_cuda("vol_confidences", vol_confidences)
+        conf = vol_confidences[:B].reshape(B, V, heatmaps.shape[2])
+    # the reference only ever indexes [batch_i, view_i] of these (op.py:108,118)
+    proj = proj_matricies[:B, :V]
+    coord = coord_volumes[:B]
+    return _Unproject.apply(heatmaps, proj, coord, conf, agg, 1 if align_corners else 0)
+
+
+class _SoftArgmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, volumes, coord, softmax, multiplier):
+        L = _lib.lib()
+        B, J = volumes.shape[:2]
+        nvox = int(volumes.shape[2]) * int(volumes.shape[3]) * int(volumes.shape[4])
+        with torch.cuda.device(volumes.device):
+            st = _stream()
+            vol = _f32c(volumes)
+            coord_c = _f32c(coord)
+            coords = torch.zeros((B, J, 3), device=vol.device, dtype=torch.float32)
+            prob = torch.empty(vol.shape, device=vol.device, dtype=torch.float32)
+            stats = torch.empty((B, J, 5), device=vol.device, dtype=torch.float32)
+            if nvox > 0:
+                nbytes = L.lt_softargmax_ws_bytes(B, J, nvox)
+                ws = torch.empty((max(nbytes, 4) // 4,), device=vol.device, dtype=torch.float32)
+                _lib.check(L.lt_softargmax_fwd(_lib.ptr(vol), _lib.ptr(coord_c), _lib.ptr(coords), _lib.ptr(prob),
+                                               _lib.ptr(stats), _lib.ptr(ws), B, J, nvox, softmax, multiplier, st))
+        ctx.save_for_backward(prob, coord_c, coords)
+        ctx.meta = (B, J, nvox, softmax, multiplier, volumes.dtype)
+        ctx.set_materialize_grads(False)
+        return coords.to(volumes.dtype), prob.to(volumes.dtype)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_coords, g_prob):
+        L = _lib.lib()
+        prob, coord_c, coords = ctx.saved_tensors
+        B, J, nvox, softmax, multiplier, dtype = ctx.meta
+        if not ctx.needs_input_grad[0]:
+            return None, None, None, None
+        with torch.cuda.device(prob.device):
+            st = _stream()
+            gvol = torch.empty_like(prob)
+            if nvox == 0 or B * J == 0:
+                return gvol.to(dtype), None, None, None
+            gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 3), device=prob.device)
+            gp = _f32c(g_prob) if g_prob is not None else None
+            dots = None
+            if gp is not None and softmax:
+                dots = torch.empty((B, J), device=prob.device, dtype=torch.float32)
+                nbytes = L.lt_softargmax_ws_bytes(B, J, nvox)
+                ws = torch.empty((max(nbytes, 4) // 4,), device=prob.device, dtype=torch.float32)
+                _lib.check(L.lt_softargmax_bwd_dot(_lib.ptr(prob), _lib.ptr(gp), _lib.ptr(dots), _lib.ptr(ws),
+                                                   B, J, nvox, st))
+            _lib.check(L.lt_softargmax_bwd(_lib.ptr(prob), _lib.ptr(coord_c), _lib.ptr(coords), _lib.ptr(gc),
+                                           _lib.ptr(gp), _lib.ptr(dots), _lib.ptr(gvol), B, J, nvox, softmax,
+                                           multiplier, st))
+        return gvol.to(dtype), None, None, None
+
+
+def integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True, *, multiplier=1.0):
+    """Soft-argmax of each joint volume in world coordinates (reference: op.py:84-96).
+
+    volumes (B,J,N0,N1,N2), coord_volumes (B,N0,N1,N2,3). Returns ``(coordinates (B,J,3), volumes (B,J,N0,N1,N2))``
+    where the second value is the softmax-normalised volume (softmax=True) or relu(volumes) un-normalised
+    (softmax=False, op.py:91). ``multiplier`` (keyword only, default 1.0) fuses the ``volumes * volume_multiplier``
+    that the caller does before the call (triangulation.py:353). Gradient flows from both outputs into ``volumes``.
+    """
+    _require_cuda("volumes", volumes)
+    _require_cuda("coord_volumes", coord_volumes)
+    if volumes.dim() != 5:
+        raise RuntimeError("volumes must be (B,J,N0,N1,N2), got {}".format(tuple(volumes.shape)))
+    B = volumes.shape[0]
+    if coord_volumes.dim() != 5 or coord_volumes.shape[-1] != 3 or coord_volumes.shape[0] != B or \
+            tuple(coord_volumes.shape[1:4]) != tuple(volumes.shape[2:]):
+        # torch.einsum("bnxyz, bxyzc -> bnc") would raise RuntimeError on mismatching operands (op.py:94)
+        raise RuntimeError("coord_volumes {} does not match volumes {}".format(
+            tuple(coord_volumes.shape), tuple(volumes.shape)))
+    multiplier = float(multiplier)
+    if not multiplier > 0.0:  # the kernels fold a positive scale into the exponent; anything else is pre-scaled
+        volumes = volumes * multiplier
+        multiplier = 1.0
+    return _SoftArgmax.apply(volumes, coord_volumes, 1 if softmax else 0, multiplier)

@@ -1,0 +1,134 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (imported in place from /root/reference) on small
+seeded inputs. Run in the authoring container only (the reference does not travel to the GPU box):
+
+    python oracle/make_golden.py
+
+Every file stores the inputs next to the reference's outputs (and autograd gradients), so the fixtures do not depend
+on the synthetic generators staying bit-stable. TEST INFRASTRUCTURE ONLY.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.environ.get("LT_REFERENCE", "/root/reference")
+sys.path.insert(0, ROOT)
+sys.path.insert(0, REF)
+
+import lt_b200  # noqa: E402  (only for lt_b200.synthetic, host-side generators)
+from mvn.utils import multiview as ref_mv  # noqa: E402
+from mvn.utils import op as ref_op  # noqa: E402
+
+syn = lt_b200.synthetic
+OUT = os.path.join(ROOT, "tests", "golden")
+warnings.filterwarnings("ignore")
+
+
+def npz(name, **arrays):
+    arrays = {k: (v.detach().cpu().numpy() if torch.is_tensor(v) else np.asarray(v)) for k, v in arrays.items()
+              if v is not None}
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print("%-40s %8.1f KiB" % (name, os.path.getsize(path) / 1024))
+
+
+def run_unproject(tag, method, align_corners, **kw):
+    conf_kind = method if method.startswith("conf") else None
+    d = syn.make_unproject_inputs(conf=conf_kind, **kw)
+    hm = d["heatmaps"].clone().requires_grad_(True)
+    vc = d["vol_confidences"].clone().requires_grad_(True) if d["vol_confidences"] is not None else None
+    saved = ref_op.F.grid_sample
+    if align_corners:  # what the reference computed under its pinned torch 1.0.1 (requirements.txt:20)
+        ref_op.F.grid_sample = lambda inp, grid: saved(inp, grid, align_corners=True)
+    try:
+        out = ref_op.unproject_heatmaps(hm, d["proj_matricies"], d["coord_volumes"], method, vc)
+        g = torch.Generator().manual_seed(kw.get("seed", 0) + 77)
+        gout = torch.randn(out.shape, generator=g)
+        out.backward(gout)
+        # the same call with float64 inputs (per-view samples still rounded to the fp32 buffers of op.py:104,111)
+        out64 = ref_op.unproject_heatmaps(d["heatmaps"].double(), d["proj_matricies"].double(),
+                                          d["coord_volumes"].double(), method,
+                                          d["vol_confidences"].double() if vc is not None else None)
+    finally:
+        ref_op.F.grid_sample = saved
+    npz("unproject_%s" % tag, heatmaps=d["heatmaps"], proj_matricies=d["proj_matricies"],
+        coord_volumes=d["coord_volumes"], vol_confidences=d["vol_confidences"], out=out, out64=out64, grad_out=gout,
+        grad_heatmaps=hm.grad, grad_vol_confidences=(vc.grad if vc is not None else None),
+        align_corners=np.array(int(align_corners)), method=np.array(method))
+
+
+def run_softargmax(tag, softmax, **kw):
+    d = syn.make_softargmax_inputs(**kw)
+    for dt, suffix in ((torch.float32, ""), (torch.float64, "64")):
+        vol = d["volumes"].to(dt).clone().requires_grad_(True)
+        coords, prob = ref_op.integrate_tensor_3d_with_coordinates(vol, d["coord_volumes"].to(dt), softmax=softmax)
+        g = torch.Generator().manual_seed(kw.get("seed", 0) + 78)
+        gc = torch.randn(coords.shape, generator=g)
+        gp = torch.randn(prob.shape, generator=g)
+        (gv_c,) = torch.autograd.grad(coords, vol, gc.to(dt), retain_graph=True)          # through coordinates only
+        (gv_b,) = torch.autograd.grad([coords, prob], vol, [gc.to(dt), gp.to(dt)])        # through both outputs
+        if suffix == "":
+            res = dict(volumes=d["volumes"], coord_volumes=d["coord_volumes"], coords=coords, prob=prob, grad_coords=gc,
+                       grad_prob=gp, grad_volumes_coords_only=gv_c, grad_volumes_both=gv_b)
+        else:
+            res.update(coords64=coords, prob64=prob, grad_volumes_coords_only64=gv_c, grad_volumes_both64=gv_b)
+    npz("softargmax_%s" % tag, softmax=np.array(int(softmax)), **res)
+
+
+def run_dlt(tag, **kw):
+    d = syn.make_dlt_inputs(**kw)
+    P, pts, conf = d["proj_matricies"], d["points"], d["confidences"]
+    pts32 = pts.clone().requires_grad_(True)
+    conf32 = conf.clone().requires_grad_(True) if conf is not None else None
+    out32 = ref_mv.triangulate_batch_of_points(P, pts32, conf32)
+    g = torch.Generator().manual_seed(kw.get("seed", 0) + 79)
+    gout = torch.randn(out32.shape, generator=g)
+    out32.backward(gout)
+    # float64 run of the reference's per-point solver (the batched wrapper rounds to fp32, multiview.py:164)
+    B, V, J = pts.shape[:3]
+    pts64 = pts.double().clone().requires_grad_(True)
+    conf64 = conf.double().clone().requires_grad_(True) if conf is not None else None
+    rows = []
+    for b in range(B):
+        for j in range(J):
+            c = conf64[b, :, j] if conf64 is not None else torch.ones(V, dtype=torch.float64)
+            rows.append(ref_mv.triangulate_point_from_multiple_views_linear_torch(P[b].double(), pts64[b, :, j], c))
+    out64 = torch.stack(rows).view(B, J, 3)
+    out64.backward(gout.double())
+    npz("dlt_%s" % tag, proj_matricies=P, points=pts, confidences=conf, points_3d=d["points_3d"], out32=out32,
+        out64=out64, grad_out=gout, grad_points32=pts32.grad, grad_points64=pts64.grad,
+        grad_confidences32=(conf32.grad if conf32 is not None else None),
+        grad_confidences64=(conf64.grad if conf64 is not None else None))
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(4)
+    small = dict(B=2, V=3, C=6, H=10, W=12, N=(5, 6, 7), seed=11, train=True, inside_view=True, side=2500.0)
+    for method in ("sum", "conf", "conf_norm", "max", "softmax"):
+        run_unproject("small_%s" % method, method, False, **small)
+    run_unproject("small_softmax_ac", "softmax", True, **small)
+    run_unproject("small_sum_ac", "sum", True, **small)
+    # 32-channel features on an 8^3 grid: the fast kernel instantiation (C=32 -> 4 lanes per voxel, aligned runs)
+    c32 = dict(B=1, V=4, C=32, H=16, W=16, N=8, seed=12, train=True, side=2500.0)
+    for method in ("sum", "conf", "max", "softmax"):
+        run_unproject("c32_%s" % method, method, False, **c32)
+    # more views than one chunk (kViewChunk = 4): exercises the many-view softmax/max paths
+    many = dict(B=1, V=7, C=8, H=16, W=16, N=(4, 8, 8), seed=13, train=True, dome=True, side=2500.0)
+    for method in ("sum", "conf", "max", "softmax"):
+        run_unproject("many_%s" % method, method, False, **many)
+    run_softargmax("small_softmax", True, B=2, J=3, N=(5, 6, 7), seed=21, train=True)
+    run_softargmax("small_relu", False, B=2, J=3, N=(5, 6, 7), seed=22, train=True)
+    run_softargmax("peaked_softmax", True, B=1, J=3, N=12, seed=23, peaked=True, train=True)
+    run_dlt("conf", B=3, V=4, J=5, seed=31)
+    run_dlt("noconf", B=2, V=3, J=4, seed=32, with_conf=False)
+    run_dlt("manyview", B=1, V=31, J=6, seed=33, dome=True)
+    run_dlt("twoview", B=2, V=2, J=3, seed=34)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,89 @@
+"""CPU: host-side behaviour of the drop-in functions that does not need a device: signatures, error conventions
+(SURVEY.md §8b), synthetic generators, slab bounds, reference patching."""
+import inspect
+import os
+import sys
+
+import pytest
+import torch
+
+import lt_b200
+from lt_b200 import slab, synthetic
+
+
+def test_signatures_match_reference():
+    sig = inspect.signature(lt_b200.op.unproject_heatmaps)
+    names = list(sig.parameters)
+    assert names[:5] == ["heatmaps", "proj_matricies", "coord_volumes", "volume_aggregation_method", "vol_confidences"]
+    assert sig.parameters["volume_aggregation_method"].default == "sum"
+    assert sig.parameters["vol_confidences"].default is None
+    assert all(sig.parameters[n].kind is inspect.Parameter.KEYWORD_ONLY for n in names[5:])
+    sig = inspect.signature(lt_b200.op.integrate_tensor_3d_with_coordinates)
+    assert list(sig.parameters)[:3] == ["volumes", "coord_volumes", "softmax"] and sig.parameters["softmax"].default is True
+    sig = inspect.signature(lt_b200.multiview.triangulate_batch_of_points)
+    assert list(sig.parameters) == ["proj_matricies_batch", "points_batch", "confidences_batch"]
+    sig = inspect.signature(lt_b200.multiview.triangulate_point_from_multiple_views_linear_torch)
+    assert list(sig.parameters) == ["proj_matricies", "points", "confidences"]
+
+
+def test_error_conventions():
+    d = synthetic.make_unproject_inputs(B=1, V=2, C=4, H=8, W=8, N=4)
+    with pytest.raises(ValueError, match="Unknown volume_aggregation_method: mean"):
+        lt_b200.unproject_heatmaps(d["heatmaps"], d["proj_matricies"], d["coord_volumes"], "mean")
+    with pytest.raises(TypeError):  # reference: vol_confidences[batch_i] on None (op.py:148)
+        lt_b200.unproject_heatmaps(d["heatmaps"], d["proj_matricies"], d["coord_volumes"], "conf_norm")
+    # no CPU fallback: CPU tensors are refused, loudly
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        lt_b200.unproject_heatmaps(d["heatmaps"], d["proj_matricies"], d["coord_volumes"], "sum")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        lt_b200.integrate_tensor_3d_with_coordinates(torch.zeros(1, 2, 4, 4, 4), d["coord_volumes"])
+    dl = synthetic.make_dlt_inputs(B=1, V=3, J=2)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        lt_b200.triangulate_batch_of_points(dl["proj_matricies"], dl["points"], dl["confidences"])
+    with pytest.raises(AssertionError):  # multiview.py:143
+        lt_b200.triangulate_point_from_multiple_views_linear_torch(dl["proj_matricies"][0], dl["points"][0, :2, 0])
+
+
+def test_synthetic_generators_are_seeded_and_shaped():
+    a = synthetic.make_unproject_inputs(B=2, V=4, C=8, H=24, W=24, N=8, seed=3, train=True, conf="conf_norm")
+    b = synthetic.make_unproject_inputs(B=2, V=4, C=8, H=24, W=24, N=8, seed=3, train=True, conf="conf_norm")
+    for k in ("heatmaps", "proj_matricies", "coord_volumes", "vol_confidences"):
+        assert torch.equal(a[k], b[k])
+    assert a["coord_volumes"].shape == (2, 8, 8, 8, 3) and a["proj_matricies"].shape == (2, 4, 3, 4)
+    assert torch.allclose(a["vol_confidences"].sum(1), torch.ones(2, 8), atol=1e-6)
+    # the cuboid is 2500 mm wide and centred on the base point
+    cv = a["coord_volumes"][0].reshape(-1, 3)
+    assert abs((cv.max(0).values - cv.min(0).values)[2].item() - 2500.0) < 1e-2
+    frac = synthetic.inside_fraction(a["proj_matricies"], a["coord_volumes"], 24, 24)
+    assert 0.4 < frac < 0.8
+    inside = synthetic.make_unproject_inputs(B=1, V=2, C=1, H=8, W=8, N=8, seed=1, inside_view=True)
+    pts = torch.cat([inside["coord_volumes"][0].reshape(-1, 3), torch.ones(512, 1)], 1)
+    depth = pts @ inside["proj_matricies"][0, 0, 2]
+    assert (depth <= 0).any() and (depth > 0).any()  # exercises the z <= 0 branch (op.py:121)
+
+
+def test_slab_bounds_partition():
+    for n0, world in ((256, 8), (64, 4), (7, 3), (5, 8)):
+        spans = [slab.slab_bounds(n0, world, r) for r in range(world)]
+        assert spans[0][0] == 0 and spans[-1][1] == n0
+        assert all(a[1] == b[0] for a, b in zip(spans[:-1], spans[1:]))
+        sizes = [hi - lo for lo, hi in spans]
+        assert max(sizes) - min(sizes) <= 1
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/mvn"), reason="reference tree not present")
+def test_patch_reference_swaps_the_three_call_sites():
+    sys.path.insert(0, "/root/reference")
+    try:
+        import mvn.utils.multiview as ref_mv
+        import mvn.utils.op as ref_op
+        orig = ref_op.unproject_heatmaps
+        done = lt_b200.patch_reference()
+        assert "mvn.utils.op.unproject_heatmaps" in done
+        assert ref_op.unproject_heatmaps is lt_b200.op.unproject_heatmaps
+        assert ref_op.integrate_tensor_3d_with_coordinates is lt_b200.op.integrate_tensor_3d_with_coordinates
+        assert ref_mv.triangulate_batch_of_points is lt_b200.multiview.triangulate_batch_of_points
+        lt_b200.unpatch_reference()
+        assert ref_op.unproject_heatmaps is orig
+    finally:
+        sys.path.remove("/root/reference")
