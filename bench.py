@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py — volumes/s, forward+backward, of the fused unproject+aggregate (K0+K1) and volumetric soft-argmax (K2)
+path on synthetic Human3.6M-shaped data (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3|cfg1|cfg4|cfg5] [--impl ours|reference]
+
+One "step" = one pass of the hot path over one batch: K0 (layout) + K1 fwd + K2 fwd + K2 bwd + K1 bwd + K0 inverse.
+`value`  : device-resident arm, direct C-ABI launches on preallocated buffers, CUDA events, max over ranks.
+`e2e`    : the public python API (lt_b200.unproject_heatmaps / integrate_tensor_3d_with_coordinates under autograd) fed
+           from PINNED HOST tensors every step (H2D inside the timed region) with the loss + coordinates read back.
+`roofline`: per-kernel CUDA-event durations taken inside the same timed loop against MEASURED_PEAKS.json.
+`cpu_baseline`: the oracle port of the reference's torch CPU path, timed on this box's host cores (rank 0, N=1).
+--impl reference prints the same line for the CPU reference arm (oracle port; the reference is pure python and its
+tree does not travel to the GPU box).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: B per GPU (weak) or total (strong), V, C, H, W, N, J, aggregation, scaling
+    "cfg3": dict(B=16, V=4, C=32, H=96, W=96, N=64, J=17, agg="softmax", scaling="weak",
+                 desc="volumetric training step: B=16/GPU, 4 views, 32ch 96x96, 64^3, softmax aggregation, fwd+bwd"),
+    "cfg1": dict(B=1, V=4, C=32, H=96, W=96, N=64, J=17, agg="softmax", scaling="weak",
+                 desc="H36M eval shape: B=1, 4 views, 32ch 96x96, 64^3, softmax aggregation, fwd+bwd"),
+    "cfg4": dict(B=8, V=31, C=32, H=96, W=96, N=64, J=17, agg="conf", scaling="strong",
+                 desc="many-view stress: B=8 total (batch-sharded), 31 views, conf aggregation, fwd+bwd"),
+    "cfg5": dict(B=1, V=4, C=32, H=96, W=96, N=256, J=17, agg="softmax", scaling="strong",
+                 desc="high-resolution volume: B=1, 4 views, 256^3 split into z-slabs, one NCCL exchange, fwd only K1 + fwd/bwd K2"),
+}
+
+
+def algorithmic_bytes(w, B):
+    """SURVEY.md §8d / BASELINE.md §3 per-kernel compulsory HBM bytes for B batch items."""
+    F = w["V"] * w["C"] * w["H"] * w["W"] * 4
+    n0 = w.get("N0", w["N"])
+    nvox = n0 * w["N"] * w["N"]
+    K, O, S = nvox * 12, w["C"] * nvox * 4, w["J"] * nvox * 4
+    return {
+        "k0_to_hwc": B * 2 * F,
+        "k1_unproject_fwd": B * (F + K + O),
+        "k2_softargmax_fwd": B * (S + K + S),
+        "k2_softargmax_bwd": B * (S + K + S),
+        "k1_unproject_bwd": B * (O + K + (0 if w["agg"] == "sum" else F) + F),
+        "k0_to_chw": B * 2 * F,
+    }
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons of this rank's GPU, sampled through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+                     "hw_power_brake_slowdown": 0x80, "sw_power_cap": 0x4}
+            while True:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    bits = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.reasons.update(k for k, m in names.items() if bits & m)
+                if self._stop_evt.wait(0.02):
+                    break
+        except Exception as e:  # NVML missing: report that instead of inventing clocks
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# device-resident arm: direct C-ABI launches on preallocated buffers
+# ---------------------------------------------------------------------------------------------------------------------
+STAGES = ["k0_to_hwc", "k1_unproject_fwd", "k2_softargmax_fwd", "k2_softargmax_bwd", "k1_unproject_bwd", "k0_to_chw"]
+LAUNCHES_PER_STEP = {"k0_to_hwc": 1, "k1_unproject_fwd": 1, "k2_softargmax_fwd": 3, "k2_softargmax_bwd": 1,
+                     "k1_unproject_bwd": 1, "k0_to_chw": 1}
+
+
+class DeviceStep:
+    """Preallocated buffers + one method that enqueues the whole step (optionally with an event after each stage)."""
+
+    def __init__(self, w, B, dev, seed):
+        import lt_b200
+        from lt_b200 import _lib, synthetic
+        self.L, self.lib, self.w, self.B, self.dev = _lib.lib(), _lib, w, B, dev
+        conf = "conf" if w["agg"] == "conf" else None
+        N = w["N"] if "N0" not in w else (w["N0"], w["N"], w["N"])
+        d = synthetic.make_unproject_inputs(B=B, V=w["V"], C=w["C"], H=w["H"], W=w["W"], N=N, seed=seed, train=True,
+                                            conf=conf, dome=w["V"] > 8)
+        g = torch.Generator().manual_seed(seed + 5)
+        self.host = d
+        self.feat = d["heatmaps"].to(dev)
+        self.proj = d["proj_matricies"].to(dev)
+        self.coord = d["coord_volumes"].to(dev)
+        self.conf = d["vol_confidences"].to(dev) if conf else None
+        self.N = tuple(self.coord.shape[1:4])
+        nvox = self.N[0] * self.N[1] * self.N[2]
+        self.nvox = nvox
+        Cp = self.L.lt_padded_channels(w["C"])
+        self.feat_hwc = torch.empty((B, w["V"], w["H"], w["W"], Cp), device=dev)
+        self.vol = torch.empty((B, w["C"]) + self.N, device=dev)
+        gd = torch.Generator(device=dev).manual_seed(seed + 6)
+        self.gvol = torch.randn((B, w["C"]) + self.N, generator=gd, device=dev)     # upstream grad of K1's output
+        self.x = torch.randn((B, w["J"]) + self.N, generator=gd, device=dev)        # V2V output stand-in, N(0,1)
+        self.coords = torch.empty((B, w["J"], 3), device=dev)
+        self.prob = torch.empty_like(self.x)
+        self.stats = torch.empty((B, w["J"], 5), device=dev)
+        self.gcoords = torch.randn((B, w["J"], 3), generator=g).to(dev)
+        self.gx = torch.empty_like(self.x)
+        self.gfeat_hwc = torch.empty_like(self.feat_hwc)
+        self.gfeat = torch.empty_like(self.feat)
+        self.gconf = torch.empty_like(self.conf) if conf else None
+        ws_bytes = max(self.L.lt_softargmax_ws_bytes(B, w["J"], nvox),
+                       self.L.lt_unproject_bwd_ws_bytes(B, w["V"], w["C"], *self.N), 4)
+        self.ws = torch.empty((ws_bytes // 4,), device=dev)
+        self.agg = {"sum": 0, "conf": 1, "max": 2, "softmax": 3}[w["agg"]]
+
+    def run(self, events=None):
+        L, p, chk, w, B = self.L, self.lib.ptr, self.lib.check, self.w, self.B
+        st = torch.cuda.current_stream().cuda_stream
+        N0, N1, N2 = self.N
+
+        def mark(i):
+            if events is not None:
+                events[i].record()
+
+        mark(0)
+        chk(L.lt_feat_to_hwc(p(self.feat), p(self.feat_hwc), B * w["V"], w["C"], w["H"], w["W"], st))
+        mark(1)
+        chk(L.lt_unproject_fwd(p(self.feat_hwc), p(self.proj), p(self.coord), p(self.conf), p(self.vol), B, w["V"],
+                               w["C"], w["H"], w["W"], N0, N1, N2, self.agg, 0, st))
+        mark(2)
+        chk(L.lt_softargmax_fwd(p(self.x), p(self.coord), p(self.coords), p(self.prob), p(self.stats), p(self.ws), B,
+                                w["J"], self.nvox, 1, 1.0, st))
+        mark(3)
+        chk(L.lt_softargmax_bwd(p(self.prob), p(self.coord), p(self.coords), p(self.gcoords), None, None, p(self.gx),
+                                B, w["J"], self.nvox, 1, 1.0, st))
+        mark(4)
+        self.gfeat_hwc.zero_()
+        chk(L.lt_unproject_bwd(p(self.gvol), p(self.feat_hwc), p(self.proj), p(self.coord), p(self.conf),
+                               p(self.gfeat_hwc), p(self.gconf), p(self.ws), B, w["V"], w["C"], w["H"], w["W"], N0, N1,
+                               N2, self.agg, 0, st))
+        mark(5)
+        chk(L.lt_feat_to_chw(p(self.gfeat_hwc), p(self.gfeat), B * w["V"], w["C"], w["H"], w["W"], st))
+        mark(6)
+
+
+class E2EStep:
+    """Public-API arm: pinned host inputs -> H2D -> unproject -> (V2V stand-in: first J channels) -> soft-argmax ->
+    L1 loss -> backward -> loss + coordinates back to the host."""
+
+    def __init__(self, dstep):
+        h, w = dstep.host, dstep.w
+        self.w, self.dev = w, dstep.dev
+        self.h_feat = h["heatmaps"].pin_memory()
+        self.h_proj = h["proj_matricies"].pin_memory()
+        self.h_coord = h["coord_volumes"].pin_memory()
+        self.h_conf = h["vol_confidences"].pin_memory() if h["vol_confidences"] is not None else None
+        self.h_target = torch.zeros(dstep.B, w["J"], 3).pin_memory()
+        self.h_loss = torch.zeros(1).pin_memory()
+        self.h_coords = torch.zeros(dstep.B, w["J"], 3).pin_memory()
+        self.h2d = sum(t.numel() * 4 for t in (self.h_feat, self.h_proj, self.h_coord, self.h_target)) + \
+            (self.h_conf.numel() * 4 if self.h_conf is not None else 0)
+        self.d2h = (self.h_loss.numel() + self.h_coords.numel()) * 4
+
+    def run(self):
+        import lt_b200
+        w, dev = self.w, self.dev
+        feat = self.h_feat.to(dev, non_blocking=True).requires_grad_(True)
+        proj = self.h_proj.to(dev, non_blocking=True)
+        coord = self.h_coord.to(dev, non_blocking=True)
+        conf = self.h_conf.to(dev, non_blocking=True) if self.h_conf is not None else None
+        target = self.h_target.to(dev, non_blocking=True)
+        vol = lt_b200.unproject_heatmaps(feat, proj, coord, w["agg"], conf)
+        x = vol[:, :w["J"]]                     # stand-in for the V2V net (stays in PyTorch, out of scope)
+        coords, _ = lt_b200.integrate_tensor_3d_with_coordinates(x, coord, softmax=True)
+        loss = (coords - target).abs().mean()
+        loss.backward()
+        self.h_loss.copy_(loss.detach().view(1), non_blocking=True)
+        self.h_coords.copy_(coords.detach(), non_blocking=True)
+        return feat.grad
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CPU reference arm (oracle port of the reference's torch CPU path): one volume (B=1) per step
+# ---------------------------------------------------------------------------------------------------------------------
+def cpu_reference_step(w, seed=0, cache={}):
+    """fwd+bwd of unproject_heatmaps and integrate_tensor_3d_with_coordinates for ONE batch item with the oracle's
+    restatement of mvn/utils/op.py (same ATen calls as the reference) on all host cores. Returns seconds."""
+    from lt_b200 import synthetic
+    from oracle import ref_ops
+    key = (w["V"], w["C"], w["N"], w["agg"], seed)
+    if key not in cache:
+        conf = "conf" if w["agg"] == "conf" else None
+        n = min(w["N"], 64)  # the 256^3 config needs 8 GiB of per-view temporaries on the CPU: sample it at 64^3
+        d = synthetic.make_unproject_inputs(B=1, V=w["V"], C=w["C"], H=w["H"], W=w["W"], N=n, seed=seed, train=True,
+                                            conf=conf, dome=w["V"] > 8)
+        g = torch.Generator().manual_seed(seed + 5)
+        cache[key] = (d, torch.randn(1, w["C"], n, n, n, generator=g), torch.randn(1, w["J"], n, n, n, generator=g),
+                      torch.randn(1, w["J"], 3, generator=g))
+    d, gvol, x, gc = cache[key]
+    t0 = time.perf_counter()
+    feat = d["heatmaps"].clone().requires_grad_(True)
+    vc = d["vol_confidences"]
+    vol = ref_ops.unproject_heatmaps(feat, d["proj_matricies"], d["coord_volumes"], w["agg"], vc)
+    vol.backward(gvol)
+    xv = x.clone().requires_grad_(True)
+    coords, prob = ref_ops.integrate_tensor_3d_with_coordinates(xv, d["coord_volumes"], softmax=True)
+    coords.backward(gc)
+    return time.perf_counter() - t0
+
+
+def run_cpu_arm(w, steps, warmup):
+    torch.set_num_threads(os.cpu_count() or 1)
+    for _ in range(warmup):
+        cpu_reference_step(w)
+    times = [cpu_reference_step(w) for _ in range(steps)]
+    total = sum(times)
+    return steps / total, total / steps, torch.get_num_threads()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded CPU sample (profiling runs)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer arm (profiling runs)")
+    args = ap.parse_args()
+    w = dict(WORKLOADS[args.workload])
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    metric = "volumes/sec fwd+bwd (unproject+aggregate + soft-argmax, %d^3, %d views, %dch)" % (w["N"], w["V"], w["C"])
+    config = {"workload": "%s: %s" % (args.workload, w["desc"]), "aggregation": w["agg"], "joints": w["J"],
+              "parallelism": "batch-sharded x%d, no data-path collective" % world,
+              "cache": None}
+    _ab = algorithmic_bytes(w, w["B"])
+    config["cache"] = ("inputs larger than L2 (per-step working set %.0f MB >> 126 MB L2)" % (sum(_ab.values()) / 2e6)
+                       if sum(_ab.values()) / 2 > 3 * 126e6 else
+                       "working set fits L2; a 256 MB buffer is rewritten between timed steps (its time is subtracted)")
+
+    if args.impl == "reference":
+        # CPU arm: rank 0 only; other ranks exit without work
+        if rank != 0:
+            return
+        steps = max(1, min(args.steps, 8))
+        vps, sec, cores = run_cpu_arm(w, steps, max(1, min(args.warmup, 1)))
+        line = {"impl": "reference", "metric": metric, "value": vps, "unit": "volumes/s", "n_gpus": args.gpus,
+                "steps": steps, "warmup": 1, "ms_per_step": sec * 1e3, "higher_is_better": True,
+                "scaling": w["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": vps, "unit": "volumes/s", "cores": cores, "kind": "port",
+                                 "sample": "%d x one batch item (B=1) fwd+bwd, oracle port of mvn/utils/op.py on torch "
+                                           "CPU; the python reference tree does not travel to the GPU box" % steps},
+                "e2e": {"value": vps, "unit": "volumes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    assert torch.cuda.is_available(), "bench.py --impl ours needs a CUDA device (there is no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    B = w["B"] if w["scaling"] == "weak" else max(1, w["B"] // world)
+    if args.workload == "cfg5":  # z-slabs: this rank's share of the first volume axis
+        from lt_b200.slab import slab_bounds
+        lo, hi = slab_bounds(w["N"], world, rank)
+        w["N0"] = hi - lo
+    total_B = B * world
+    step = DeviceStep(w, B, dev, seed=rank)
+    flush = None if "larger" in config["cache"] else torch.empty(64 * 1024 * 1024, device=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, per_stage):
+        for _ in range(warmup):
+            fn(None)
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 1)] for _ in range(steps)] \
+            if per_stage else None
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        flush_ms = 0.0
+        t0.record()
+        for i in range(steps):
+            if flush is not None:
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(); flush.fill_(float(i)); b.record()
+                evs and evs[i].append((a, b))
+            fn(evs[i] if evs else None)
+        t1.record()
+        barrier()
+        clocks = sampler.stop()
+        ms = t0.elapsed_time(t1)
+        if flush is not None and evs:
+            flush_ms = sum(e[-1][0].elapsed_time(e[-1][1]) for e in evs)
+        ms -= flush_ms
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms, evs, clocks
+
+    ms, evs, clocks = timed(lambda e: step.run(e), args.steps, args.warmup, True)
+    value = total_B * args.steps / (ms * 1e-3)
+
+    # per-kernel durations from the events of the timed loop (rank 0's GPU)
+    peak, peak_src = measured_peaks()
+    abytes = algorithmic_bytes(w, B)
+    kernels = {}
+    for si, name in enumerate(STAGES):
+        dur = sum(e[si].elapsed_time(e[si + 1]) for e in evs) / args.steps
+        gbs = abytes[name] / (dur * 1e-3) / 1e9 if dur > 0 else 0.0
+        kernels[name] = {"ms": round(dur, 4), "algorithmic_bytes": abytes[name], "gbs": round(gbs, 1),
+                         "frac": round(gbs / peak, 4), "share": round(dur / (ms / args.steps), 4)}
+    top = max(kernels, key=lambda k: kernels[k]["ms"])
+    total_bytes = sum(abytes[k] for k in STAGES if not k.startswith("k0"))  # K0 is our own layout overhead
+    path_gbs = total_bytes / (ms / args.steps * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": top, "achieved": kernels[top]["gbs"], "peak": peak, "unit": "GB/s",
+                "frac": kernels[top]["frac"], "traffic": None, "peak_source": peak_src,
+                "whole_step": {"achieved": round(path_gbs, 1), "frac": round(path_gbs / peak, 4),
+                               "note": "algorithmic bytes of K1 fwd/bwd + K2 fwd/bwd over the whole step time"},
+                "kernels": kernels}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            roofline["traffic"] = json.load(open(traffic_file)).get(args.workload, {}).get(top)
+        except Exception:
+            pass
+
+    e2e = None
+    if not args.no_e2e:
+        es = E2EStep(step)
+        e_steps = max(3, min(args.steps, 10))
+        ems, _, _ = timed(lambda e: es.run(), e_steps, 3, False)
+        e2e = {"value": total_B * e_steps / (ems * 1e-3), "unit": "volumes/s", "h2d_bytes_per_step": es.h2d,
+               "d2h_bytes_per_step": es.d2h, "steps": e_steps, "ms_per_step": ems / e_steps}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        vps, sec, cores = run_cpu_arm(w, 5, 1)
+        cpu_baseline = {"value": vps, "unit": "volumes/s", "cores": cores, "kind": "port",
+                        "sample": "5 x one batch item (B=1) fwd+bwd of the same workload, oracle port of "
+                                  "mvn/utils/op.py (torch CPU, all host threads)"}
+    if rank == 0:
+        line = {"metric": metric, "value": value, "unit": "volumes/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": w["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": sum(LAUNCHES_PER_STEP.values()) * args.steps,
+                "roofline": roofline, "cpu_baseline": cpu_baseline}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

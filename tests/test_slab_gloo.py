@@ -38,7 +38,8 @@ def _worker(rank, world, port, name, with_gp, q):
         gp = g["grad_prob"][:, :, lo:hi] if with_gp else None
         outs, grads = ([coords, prob], [g["grad_coords"], gp]) if with_gp else ([coords], [g["grad_coords"]])
         (gv,) = torch.autograd.grad(outs, vol, grads)
-        q.put((rank, lo, hi, coords.detach(), prob.detach(), gv))
+        # plain numpy through the queue: torch tensors travel by fd-sharing, which races with worker exit
+        q.put((rank, lo, hi, coords.detach().numpy().copy(), prob.detach().numpy().copy(), gv.numpy().copy()))
     finally:
         dist.destroy_process_group()
 
@@ -55,6 +56,7 @@ def test_sharded_softargmax_matches_unsharded_reference(world, name, with_gp):
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    res = [(r, lo, hi, torch.from_numpy(c), torch.from_numpy(p_), torch.from_numpy(g_)) for r, lo, hi, c, p_, g_ in res]
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
