@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_stats(const float* __restri
 #pragma unroll
   for (int i = 0; i < kSamEpt / 4; ++i) {
     const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
-    ok[i] = VEC ? (v0 < nvox) : (v0 + 3 < nvox);
+    ok[i] = VEC && (v0 < nvox);  // rows are only 16-byte aligned when nvox % 4 == 0
     if (ok[i]) {
       const float4* p = reinterpret_cast<const float4*>(cb + v0 * 3);
       float4 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
