@@ -54,11 +54,10 @@ __global__ void __launch_bounds__(256) k_feat_layout(const float* __restrict__ s
 }
 
 int padded_channels(int C) {
-  // 8 channels per lane and 4/8/16/32 lanes per voxel (unproject.cuh); above 256, blocks of 256 channels
+  // 4 channels per lane and 8/16/32 lanes per voxel (unproject.cuh); above 128, blocks of 128 channels
   if (C <= 32) return 32;
   if (C <= 64) return 64;
-  if (C <= 128) return 128;
-  return ((C + 255) / 256) * 256;
+  return ((C + 127) / 128) * 128;
 }
 
 cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwc,

@@ -1,13 +1,16 @@
 // unproject.cuh — geometry shared by the K1 forward and backward kernels.
 //
 // Work decomposition (both directions)
-//   * a lane owns kCPL = 8 consecutive channels; LPV = Cp/8 lanes (4 for the 32-channel features of
-//     triangulation.py:239) cover one texel, so one tap is ONE contiguous Cp*4-byte read (LDG.E.256 per
-//     lane, 1 L1 wavefront per 128 B) and a warp works on G = 32/LPV voxels at a time;
+//   * a lane owns kCPL = 4 consecutive channels; LPV = Cp/4 lanes (8 for the 32-channel features of
+//     triangulation.py:239) cover one texel, so one tap is ONE contiguous Cp*4-byte access per lane group:
+//     LDG.E.128 per lane = one full 128-byte line per voxel in the forward gather, and one
+//     REDG.E.ADD.F32x4 per lane = four complete 32-byte sectors per voxel in the backward scatter (the L2
+//     reduction unit retires one sector per cycle per slice, so half-filled sectors would halve its rate);
 //   * a lane group walks a run of kRun = 8 consecutive voxels along the fastest volume axis, so that the
 //     8 results of one channel leave as one full 32-byte sector (STG.E.256);
-//   * a CTA (8 warps) covers a compact (4*G0)x(2*G1)x8 block of the volume (8x8x8 for C=32): the block's
-//     image footprint (~17x17 texels per view at Human3.6M geometry) is what has to stay in L1;
+//   * a warp owns a 2x4 block of runs and works on G = 32/LPV of them per round (R = 8/G rounds);
+//   * a CTA (8 warps, 4x2) therefore always covers a compact 8x8x8 block of the volume: its image footprint
+//     (~17x17 texels per view at Human3.6M geometry) is what has to stay in L1;
 //   * projection (mvn/utils/multiview.py:80-101 + op.py:121-130 + the index arithmetic of
 //     F.grid_sample) is done ONCE per (voxel, view) by one lane ("phase A") and handed to the gather
 //     lanes through a per-warp shared-memory descriptor table (offset + 4 tap weights).
@@ -18,10 +21,13 @@
 namespace lt {
 
 constexpr int kRun = 8;           // voxels per lane-group run
-constexpr int kCPL = 8;           // channels per lane
+constexpr int kCPL = 4;           // channels per lane
 constexpr int kWarpsPerCta = 8;   // arranged 4 (axis 0) x 2 (axis 1)
+constexpr int kWarpRuns0 = 2, kWarpRuns1 = 4;  // runs owned by a warp: 2 (axis 0) x 4 (axis 1)
+constexpr int kTile0 = 4 * kWarpRuns0, kTile1 = 2 * kWarpRuns1;  // CTA tile 8 x 8 (x 8 along the run axis)
 constexpr int kViewChunk = 4;     // views resolved per phase-A round
 constexpr int kMaxViewsSmem = 64; // projection matrices staged per CTA
+constexpr int kMaxLanesPerVoxel = 32;  // => channel blocks of 128
 
 constexpr int kOffMask = 0x0fffffff;
 constexpr int kOffDx = 1 << 28;   // second column tap is a distinct texel
@@ -29,12 +35,12 @@ constexpr int kOffDy = 1 << 29;   // second row tap is a distinct texel
 
 template <int LPV>
 struct TileGeom {
-  static constexpr int G = 32 / LPV;          // voxels (runs) in flight per warp
-  static constexpr int G1 = G < 4 ? G : 4;    // runs along axis 1
-  static constexpr int G0 = G / G1;           // runs along axis 0
-  static constexpr int T0 = 4 * G0;           // CTA tile extent, axis 0
-  static constexpr int T1 = 2 * G1;           // CTA tile extent, axis 1
-  static constexpr int kSlots = G * kRun;     // descriptor slots per warp and view
+  static constexpr int G = 32 / LPV;                              // runs in flight per warp
+  static constexpr int R = (kWarpRuns0 * kWarpRuns1) / G;         // rounds per warp
+  static constexpr int kSlots = G * kRun;                         // descriptor slots per warp, view and round
+  // run index (0..7) of lane group g in round r -> offsets inside the warp's 2x4 block
+  __device__ static __forceinline__ int run0(int r, int g) { return (r * G + g) / kWarpRuns1; }
+  __device__ static __forceinline__ int run1(int r, int g) { return (r * G + g) % kWarpRuns1; }
 };
 
 struct UnprojArgs {
@@ -93,6 +99,81 @@ __device__ __forceinline__ void make_desc(float x, float y, float z, const float
   off = (yb * W + xb) * Cp;
   if (okx0 && okx1) off |= kOffDx;
   if (oky0 && oky1) off |= kOffDy;
+}
+
+constexpr float kNoView = -1.0e30f;  // sample value of a view that does not exist (softmax weight underflows to 0)
+
+struct TileId {
+  int b, cb, t0, t1, t2, lin;
+};
+// blockIdx.x = ((b*ncb + cb)*nt0 + t0)*nt1*nt2 + t1*nt2 + t2
+__device__ __forceinline__ TileId decode_tile(const UnprojArgs& a) {
+  TileId r;
+  int t = blockIdx.x;
+  r.t2 = t % a.nt2; t /= a.nt2;
+  r.t1 = t % a.nt1; t /= a.nt1;
+  r.t0 = t % a.nt0; t /= a.nt0;
+  r.cb = t % a.ncb;
+  r.b = t / a.ncb;
+  r.lin = (r.t0 * a.nt1 + r.t1) * a.nt2 + r.t2;
+  return r;
+}
+
+// phase A: descriptors of this warp's round-r voxels x nv views -> per-warp smem table.
+// zsel < 0: all 8 z steps, slot = j*G + g (G*8 slots, one per lane for C=32); zsel >= 0: only that z step, slot = g.
+template <int LPV>
+__device__ __forceinline__ void build_descs(const UnprojArgs& a, int b, int i0_warp, int i1_warp, int z0, int r,
+                                            const float4* s_proj, float4 (*s_w)[TileGeom<LPV>::kSlots],
+                                            int (*s_off)[TileGeom<LPV>::kSlots], int v0, int nv, int zsel, int lane,
+                                            float invH, float invW) {
+  using TG = TileGeom<LPV>;
+  constexpr int G = TG::G;
+  const float* coord_b = a.coord + (size_t)b * a.nvox * 3;
+  const int nslots = zsel < 0 ? TG::kSlots : G;
+  for (int slot = lane; slot < nslots; slot += 32) {
+    const int j = zsel < 0 ? slot / G : zsel, gg = slot % G;
+    const int vi0 = i0_warp + TG::run0(r, gg), vi1 = i1_warp + TG::run1(r, gg), vz = z0 + j;
+    const bool ok = (vi0 < a.N0) && (vi1 < a.N1) && (vz < a.N2);
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (ok) {
+      const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
+      x = __ldg(cp); y = __ldg(cp + 1); z = __ldg(cp + 2);
+    }
+    for (int vv = 0; vv < nv; ++vv) {
+      int off = -1;
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ok) {
+        const int v = v0 + vv;
+        float4 r0, r1, r2;
+        if (v < kMaxViewsSmem) {
+          r0 = s_proj[v * 3]; r1 = s_proj[v * 3 + 1]; r2 = s_proj[v * 3 + 2];
+        } else {
+          const float4* pp = reinterpret_cast<const float4*>(a.proj) + ((size_t)b * a.V + v) * 3;
+          r0 = __ldg(pp); r1 = __ldg(pp + 1); r2 = __ldg(pp + 2);
+        }
+        make_desc(x, y, z, r0, r1, r2, a.H, a.W, a.Cp, invH, invW, a.align_corners, off, w);
+      }
+      s_w[vv][slot] = w;
+      s_off[vv][slot] = off;
+    }
+  }
+}
+
+// per-lane gather of one tap set: 4 x LDG.E.128 (4 channels each; the LPV lanes of a voxel read one full texel)
+// and the bilinear blend, accumulated in the nw, ne, sw, se order of ATen's grid_sampler_2d.
+__device__ __forceinline__ void gather4(const float* __restrict__ fv, int off, const float4& w, int Cp,
+                                        int rowStride, float (&s)[kCPL]) {
+  const float* p = fv + (off & kOffMask);
+  const int dx = (off & kOffDx) ? Cp : 0;
+  const int dy = (off & kOffDy) ? rowStride : 0;
+  const float4 t00 = ldg128_nc(p);
+  const float4 t01 = ldg128_nc(p + dx);
+  const float4 t10 = ldg128_nc(p + dy);
+  const float4 t11 = ldg128_nc(p + dy + dx);
+  s[0] = fmaf(t11.x, w.w, fmaf(t10.x, w.z, fmaf(t01.x, w.y, t00.x * w.x)));
+  s[1] = fmaf(t11.y, w.w, fmaf(t10.y, w.z, fmaf(t01.y, w.y, t00.y * w.x)));
+  s[2] = fmaf(t11.z, w.w, fmaf(t10.z, w.z, fmaf(t01.z, w.y, t00.z * w.x)));
+  s[3] = fmaf(t11.w, w.w, fmaf(t10.w, w.z, fmaf(t01.w, w.y, t00.w * w.x)));
 }
 
 void fill_unproj_tiling(UnprojArgs& a, int lpv);

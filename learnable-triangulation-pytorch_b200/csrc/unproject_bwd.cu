@@ -4,7 +4,8 @@
 // (V,C,N^3) temporaries and the softmax/mul/sum graph of mvn/utils/op.py:147-159. Here one launch
 // re-derives the per-view samples (never stored by the forward), forms d out / d sample_v analytically
 // and scatter-adds weight*grad into the channels-last gradient map with 16-byte vector reductions
-// (REDG.E.ADD.F32x4): 4 lanes x 2 reductions cover one 32-channel texel.
+// (REDG.E.ADD.F32x4): the 8 lanes of a voxel cover one 32-channel texel = four complete 32-byte sectors per
+// instruction, which is what the L2 reduction unit (1 sector / cycle / slice) wants.
 //   sum     : d s_v = g
 //   conf    : d s_v = conf_v * g ;  d conf_v = sum_voxels g * s_v
 //   softmax : out = sum_v s_v p_v, p = softmax_v(s)  =>  d s_v = g * p_v * (1 + s_v - out)
@@ -17,381 +18,317 @@ namespace lt {
 
 constexpr int kConfSlots = 64;  // grad_conf partial-sum slots per batch item
 
-__device__ __forceinline__ void gather8(const float* __restrict__ fv, int off, const float4& w, int Cp,
-                                        int rowStride, float (&s)[kCPL]) {
-  const float* p = fv + (off & kOffMask);
-  const int dx = (off & kOffDx) ? Cp : 0;
-  const int dy = (off & kOffDy) ? rowStride : 0;
-  f8 t00 = ldg256_nc(p);
-  f8 t01 = ldg256_nc(p + dx);
-  f8 t10 = ldg256_nc(p + dy);
-  f8 t11 = ldg256_nc(p + dy + dx);
-#pragma unroll
-  for (int k = 0; k < kCPL; ++k) {
-    float a = t00.v[k] * w.x;
-    a = fmaf(t01.v[k], w.y, a);
-    a = fmaf(t10.v[k], w.z, a);
-    a = fmaf(t11.v[k], w.w, a);
-    s[k] = a;
-  }
-}
-
-// scatter-add w_tap * d[0..7] into the four taps; taps with zero weight (outside the map) are skipped.
-__device__ __forceinline__ void scatter8(float* __restrict__ gv, int off, const float4& w, int Cp,
+// scatter-add w_tap * d[0..3] into the four taps; taps with zero weight (outside the map) are skipped.
+__device__ __forceinline__ void scatter4(float* __restrict__ gv, int off, const float4& w, int Cp,
                                          int rowStride, const float (&d)[kCPL]) {
   float* p = gv + (off & kOffMask);
   const int dx = (off & kOffDx) ? Cp : 0;
   const int dy = (off & kOffDy) ? rowStride : 0;
-  if (w.x != 0.f) {
-    red_add_v4(p, d[0] * w.x, d[1] * w.x, d[2] * w.x, d[3] * w.x);
-    red_add_v4(p + 4, d[4] * w.x, d[5] * w.x, d[6] * w.x, d[7] * w.x);
-  }
-  if (w.y != 0.f) {
-    red_add_v4(p + dx, d[0] * w.y, d[1] * w.y, d[2] * w.y, d[3] * w.y);
-    red_add_v4(p + dx + 4, d[4] * w.y, d[5] * w.y, d[6] * w.y, d[7] * w.y);
-  }
-  if (w.z != 0.f) {
-    red_add_v4(p + dy, d[0] * w.z, d[1] * w.z, d[2] * w.z, d[3] * w.z);
-    red_add_v4(p + dy + 4, d[4] * w.z, d[5] * w.z, d[6] * w.z, d[7] * w.z);
-  }
-  if (w.w != 0.f) {
-    red_add_v4(p + dy + dx, d[0] * w.w, d[1] * w.w, d[2] * w.w, d[3] * w.w);
-    red_add_v4(p + dy + dx + 4, d[4] * w.w, d[5] * w.w, d[6] * w.w, d[7] * w.w);
-  }
+  if (w.x != 0.f) red_add_v4(p, d[0] * w.x, d[1] * w.x, d[2] * w.x, d[3] * w.x);
+  if (w.y != 0.f) red_add_v4(p + dx, d[0] * w.y, d[1] * w.y, d[2] * w.y, d[3] * w.y);
+  if (w.z != 0.f) red_add_v4(p + dy, d[0] * w.z, d[1] * w.z, d[2] * w.z, d[3] * w.z);
+  if (w.w != 0.f) red_add_v4(p + dy + dx, d[0] * w.w, d[1] * w.w, d[2] * w.w, d[3] * w.w);
 }
 
-struct BwdTile {
-  int b, cb, i0_warp, i1_warp, z0, i0, i1, tile_lin;
-  bool run_ok;
-  long long run_base;
+// common prologue of the backward kernels
+struct BwdCtx {
+  int warp, lane, g, q, i0_warp, i1_warp, z0, c_lane, rowStride;
+  size_t viewStride;
+  float invH, invW;
+  const float* fb;
+  float* gb;
 };
 
 template <int LPV>
-__device__ __forceinline__ BwdTile decode_tile(const UnprojArgs& a, int warp, int g) {
-  using TG = TileGeom<LPV>;
-  BwdTile r;
-  int t = blockIdx.x;
-  const int t2 = t % a.nt2; t /= a.nt2;
-  const int t1 = t % a.nt1; t /= a.nt1;
-  const int t0 = t % a.nt0; t /= a.nt0;
-  r.cb = t % a.ncb;
-  r.b = t / a.ncb;
-  r.tile_lin = (t0 * a.nt1 + t1) * a.nt2 + t2;
-  r.i0_warp = t0 * TG::T0 + (warp >> 1) * TG::G0;
-  r.i1_warp = t1 * TG::T1 + (warp & 1) * TG::G1;
-  r.z0 = t2 * kRun;
-  r.i0 = r.i0_warp + g / TG::G1;
-  r.i1 = r.i1_warp + g % TG::G1;
-  r.run_ok = (r.i0 < a.N0) && (r.i1 < a.N1);
-  r.run_base = ((long long)r.i0 * a.N1 + r.i1) * a.N2 + r.z0;
-  return r;
+__device__ __forceinline__ BwdCtx bwd_prologue(const UnprojArgs& a, const TileId& T, float4* s_proj) {
+  BwdCtx c;
+  c.warp = threadIdx.x >> 5; c.lane = threadIdx.x & 31;
+  c.g = c.lane / LPV; c.q = c.lane % LPV;
+  for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
+    s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
+  __syncthreads();
+  c.i0_warp = T.t0 * kTile0 + (c.warp >> 1) * kWarpRuns0;
+  c.i1_warp = T.t1 * kTile1 + (c.warp & 1) * kWarpRuns1;
+  c.z0 = T.t2 * kRun;
+  c.invH = 1.f / (float)a.H; c.invW = 1.f / (float)a.W;
+  c.rowStride = a.W * a.Cp;
+  c.viewStride = (size_t)a.H * a.W * a.Cp;
+  c.c_lane = T.cb * (LPV * kCPL) + c.q * kCPL;
+  c.fb = a.feat + (size_t)T.b * a.V * c.viewStride + c.c_lane;
+  c.gb = a.gfeat + (size_t)T.b * a.V * c.viewStride + c.c_lane;
+  return c;
 }
 
-// phase A (same descriptors as the forward) for `nslots` voxel slots x nv views of this warp.
-// zsel < 0: all 8 z steps (slot = j*G + g); zsel >= 0: only z step zsel (slot = g).
-template <int LPV>
-__device__ __forceinline__ void build_descs(const UnprojArgs& a, const BwdTile& T, const float4* s_proj,
-                                            float4 (*s_w)[TileGeom<LPV>::kSlots],
-                                            int (*s_off)[TileGeom<LPV>::kSlots], int v0, int nv, int zsel,
-                                            int lane, float invH, float invW) {
-  using TG = TileGeom<LPV>;
-  constexpr int G = TG::G;
-  const float* coord_b = a.coord + (size_t)T.b * a.nvox * 3;
-  const int nslots = zsel < 0 ? TG::kSlots : G;
-  for (int slot = lane; slot < nslots; slot += 32) {
-    const int j = zsel < 0 ? slot / G : zsel, gg = slot % G;
-    const int vi0 = T.i0_warp + gg / TG::G1, vi1 = T.i1_warp + gg % TG::G1, vz = T.z0 + j;
-    const bool ok = (vi0 < a.N0) && (vi1 < a.N1) && (vz < a.N2);
-    float x = 0.f, y = 0.f, z = 0.f;
-    if (ok) {
-      const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
-      x = __ldg(cp); y = __ldg(cp + 1); z = __ldg(cp + 2);
-    }
-    for (int vv = 0; vv < nv; ++vv) {
-      int off = -1;
-      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (ok) {
-        const int v = v0 + vv;
-        float4 r0, r1, r2;
-        if (v < kMaxViewsSmem) {
-          r0 = s_proj[v * 3]; r1 = s_proj[v * 3 + 1]; r2 = s_proj[v * 3 + 2];
-        } else {
-          const float4* pp = reinterpret_cast<const float4*>(a.proj) + ((size_t)T.b * a.V + v) * 3;
-          r0 = __ldg(pp); r1 = __ldg(pp + 1); r2 = __ldg(pp + 2);
-        }
-        make_desc(x, y, z, r0, r1, r2, a.H, a.W, a.Cp, invH, invW, a.align_corners, off, w);
+// upstream gradient of this lane's 4 channels x 8 voxels: read once with 256-bit streaming loads, parked in the
+// lane's private smem slots so that the z loop can stay rolled (see unproject_fwd.cu).
+template <bool ALIGNED>
+__device__ __forceinline__ void stage_grad_out(const UnprojArgs& a, int b, int c_lane, int i0, int i1, int z0,
+                                               bool run_ok, float4 (*s_go)[32], int lane) {
+  float go[kCPL][kRun];
+  const float* gp = a.gout + (size_t)b * a.C * a.nvox + ((long long)i0 * a.N1 + i1) * a.N2 + z0;
+#pragma unroll
+  for (int k = 0; k < kCPL; ++k) {
+    const int c = c_lane + k;
+    if (run_ok && c < a.C) {
+      if (ALIGNED) {
+        const f8 t = ldg256_stream(gp + (size_t)c * a.nvox);
+#pragma unroll
+        for (int j = 0; j < kRun; ++j) go[k][j] = t.v[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < kRun; ++j) go[k][j] = (z0 + j < a.N2) ? __ldg(gp + (size_t)c * a.nvox + j) : 0.f;
       }
-      s_w[vv][slot] = w;
-      s_off[vv][slot] = off;
+    } else {
+#pragma unroll
+      for (int j = 0; j < kRun; ++j) go[k][j] = 0.f;
     }
   }
+#pragma unroll
+  for (int j = 0; j < kRun; ++j) s_go[j][lane] = make_float4(go[0][j], go[1][j], go[2][j], go[3][j]);
 }
 
 // sum / conf for any V; softmax / max for V <= kViewChunk (all samples of a voxel live in registers).
 template <int LPV, int AGG, bool ALIGNED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 1) k_unproject_bwd(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
-  __shared__ float4 s_proj[kMaxViewsSmem * 3];
-  __shared__ float4 s_w[kWarpsPerCta][kViewChunk][SLOTS];
-  __shared__ int s_off[kWarpsPerCta][kViewChunk][SLOTS];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float4* s_proj = reinterpret_cast<float4*>(smem_raw);
+  auto s_w = reinterpret_cast<float4(*)[kViewChunk][SLOTS]>(s_proj + kMaxViewsSmem * 3);
+  auto s_go = reinterpret_cast<float4(*)[kRun][32]>(&s_w[kWarpsPerCta][0][0]);
+  auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = lane / LPV, q = lane % LPV;
-  const BwdTile T = decode_tile<LPV>(a, warp, g);
+  const TileId T = decode_tile(a);
+  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj);
+  const int warp = c.warp, lane = c.lane, g = c.g;
 
-  for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
-    s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
-  __syncthreads();
+#pragma unroll 1
+  for (int r = 0; r < TG::R; ++r) {
+    const int i0 = c.i0_warp + TG::run0(r, g), i1 = c.i1_warp + TG::run1(r, g);
+    const bool run_ok = (i0 < a.N0) && (i1 < a.N1);
+    stage_grad_out<ALIGNED>(a, T.b, c.c_lane, i0, i1, c.z0, run_ok, s_go[warp], lane);
 
-  const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
-  const int rowStride = a.W * a.Cp;
-  const size_t viewStride = (size_t)a.H * a.W * a.Cp;
-  const size_t lane_choff = (size_t)T.cb * (LPV * kCPL) + q * kCPL;
-  const float* fb = a.feat + (size_t)T.b * a.V * viewStride + lane_choff;
-  float* gb = a.gfeat + (size_t)T.b * a.V * viewStride + lane_choff;
-  const int c_lane = (int)lane_choff;
+#pragma unroll 1
+    for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
+      const int nv = min(kViewChunk, a.V - v0);
+      __syncwarp();
+      build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane,
+                       c.invH, c.invW);
+      __syncwarp();
 
-  // upstream gradient of this lane's 8 channels x 8 voxels (read once: streaming loads)
-  float go[kCPL][kRun];
-  {
-    const float* gp = a.gout + (size_t)T.b * a.C * a.nvox + T.run_base;
+      float cw[kViewChunk][kCPL];   // conf of this chunk            (conf only)
+      float gcw[kViewChunk][kCPL];  // running d conf of this chunk  (conf only)
+      if (AGG == kAggConf) {
 #pragma unroll
-    for (int k = 0; k < kCPL; ++k) {
-      const int c = c_lane + k;
-      if (T.run_ok && c < a.C) {
-        if (ALIGNED) {
-          f8 t = ldg256_stream(gp + (size_t)c * a.nvox);
+        for (int vv = 0; vv < kViewChunk; ++vv)
 #pragma unroll
-          for (int j = 0; j < kRun; ++j) go[k][j] = t.v[j];
-        } else {
-#pragma unroll
-          for (int j = 0; j < kRun; ++j) go[k][j] = (T.z0 + j < a.N2) ? __ldg(gp + (size_t)c * a.nvox + j) : 0.f;
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < kRun; ++j) go[k][j] = 0.f;
+          for (int k = 0; k < kCPL; ++k) {
+            const int ch = c.c_lane + k;
+            cw[vv][k] = (vv < nv && ch < a.C) ? __ldg(a.conf + ((size_t)T.b * a.V + v0 + vv) * a.C + ch) : 0.f;
+            gcw[vv][k] = 0.f;
+          }
       }
-    }
-  }
 
-  for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
-    const int nv = min(kViewChunk, a.V - v0);
-    __syncwarp();
-    build_descs<LPV>(a, T, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane, invH, invW);
-    __syncwarp();
-
-    float cw[kViewChunk][kCPL];   // conf of this chunk            (conf only)
-    float gcw[kViewChunk][kCPL];  // running d conf of this chunk  (conf only)
-    if (AGG == kAggConf) {
+#pragma unroll 2
+      for (int j = 0; j < kRun; ++j) {
+        const int slot = j * G + g;
+        const float4 gj = s_go[warp][j][lane];
+        const float go[kCPL] = {gj.x, gj.y, gj.z, gj.w};
+        if (AGG == kAggSum || AGG == kAggConf) {
 #pragma unroll
-      for (int vv = 0; vv < kViewChunk; ++vv)
+          for (int vv = 0; vv < kViewChunk; ++vv) {
+            if (vv < nv) {
+              const int off = s_off[warp][vv][slot];
+              if (off >= 0) {
+                const float4 w = s_w[warp][vv][slot];
+                float d[kCPL];
+                if (AGG == kAggConf) {
+                  float s[kCPL];
+                  gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, s);
 #pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          const int c = c_lane + k;
-          cw[vv][k] = (vv < nv && c < a.C) ? __ldg(a.conf + ((size_t)T.b * a.V + v0 + vv) * a.C + c) : 0.f;
-          gcw[vv][k] = 0.f;
-        }
-    }
-
+                  for (int k = 0; k < kCPL; ++k) {
+                    gcw[vv][k] = fmaf(go[k], s[k], gcw[vv][k]);
+                    d[k] = cw[vv][k] * go[k];
+                  }
+                } else {
 #pragma unroll
-    for (int j = 0; j < kRun; ++j) {
-      const int slot = j * G + g;
-      if (AGG == kAggSum || AGG == kAggConf) {
-#pragma unroll
-        for (int vv = 0; vv < kViewChunk; ++vv) {
-          if (vv < nv) {
-            const int off = s_off[warp][vv][slot];
-            if (off >= 0) {
-              const float4 w = s_w[warp][vv][slot];
-              float d[kCPL];
-              if (AGG == kAggConf) {
-                float s[kCPL];
-                gather8(fb + (size_t)(v0 + vv) * viewStride, off, w, a.Cp, rowStride, s);
-#pragma unroll
-                for (int k = 0; k < kCPL; ++k) {
-                  gcw[vv][k] = fmaf(go[k][j], s[k], gcw[vv][k]);
-                  d[k] = cw[vv][k] * go[k][j];
+                  for (int k = 0; k < kCPL; ++k) d[k] = go[k];
                 }
-              } else {
-#pragma unroll
-                for (int k = 0; k < kCPL; ++k) d[k] = go[k][j];
+                scatter4(c.gb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, d);
               }
-              scatter8(gb + (size_t)(v0 + vv) * viewStride, off, w, a.Cp, rowStride, d);
             }
           }
-        }
-      } else {
-        // softmax / max over <= kViewChunk views, all samples in registers
-        float s[kViewChunk][kCPL];
-        int offs[kViewChunk];
+        } else {
+          // softmax / max over <= kViewChunk views, all samples in registers
+          float s[kViewChunk][kCPL];
+          int offs[kViewChunk];
 #pragma unroll
-        for (int vv = 0; vv < kViewChunk; ++vv) {
+          for (int vv = 0; vv < kViewChunk; ++vv) {
+            const float fill = (vv < nv) ? 0.f : kNoView;
 #pragma unroll
-          for (int k = 0; k < kCPL; ++k) s[vv][k] = 0.f;
-          offs[vv] = -1;
-          if (vv < nv) {
-            offs[vv] = s_off[warp][vv][slot];
-            if (offs[vv] >= 0)
-              gather8(fb + (size_t)(v0 + vv) * viewStride, offs[vv], s_w[warp][vv][slot], a.Cp, rowStride, s[vv]);
-          }
-        }
-        float d[kViewChunk][kCPL];
-#pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          float m = s[0][k];
-          int am = 0;
-#pragma unroll
-          for (int vv = 1; vv < kViewChunk; ++vv)
-            if (vv < nv && s[vv][k] > m) { m = s[vv][k]; am = vv; }
-          if (AGG == kAggSoftmax) {
-            float e[kViewChunk], den = 0.f;
-#pragma unroll
-            for (int vv = 0; vv < kViewChunk; ++vv) {
-              e[vv] = (vv < nv) ? expf(s[vv][k] - m) : 0.f;
-              den += e[vv];
+            for (int k = 0; k < kCPL; ++k) s[vv][k] = fill;
+            offs[vv] = -1;
+            if (vv < nv) {
+              offs[vv] = s_off[warp][vv][slot];
+              if (offs[vv] >= 0)
+                gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, offs[vv], s_w[warp][vv][slot], a.Cp, c.rowStride, s[vv]);
             }
-            const float inv = __fdiv_rn(1.f, den);
-            float o = 0.f;
-#pragma unroll
-            for (int vv = 0; vv < kViewChunk; ++vv) o = fmaf(s[vv][k], e[vv] * inv, o);
-#pragma unroll
-            for (int vv = 0; vv < kViewChunk; ++vv) d[vv][k] = go[k][j] * (e[vv] * inv) * (1.f + s[vv][k] - o);
-          } else {
-#pragma unroll
-            for (int vv = 0; vv < kViewChunk; ++vv) d[vv][k] = (vv == am) ? go[k][j] : 0.f;
           }
-        }
+          float d[kViewChunk][kCPL];
 #pragma unroll
-        for (int vv = 0; vv < kViewChunk; ++vv)
-          if (vv < nv && offs[vv] >= 0)
-            scatter8(gb + (size_t)(v0 + vv) * viewStride, offs[vv], s_w[warp][vv][slot], a.Cp, rowStride, d[vv]);
+          for (int k = 0; k < kCPL; ++k) {
+            float m = s[0][k];
+            int am = 0;
+#pragma unroll
+            for (int vv = 1; vv < kViewChunk; ++vv)
+              if (s[vv][k] > m) { m = s[vv][k]; am = vv; }
+            if (AGG == kAggSoftmax) {
+              float e[kViewChunk], den = 0.f, num = 0.f;
+#pragma unroll
+              for (int vv = 0; vv < kViewChunk; ++vv) {
+                e[vv] = fast_ex2((s[vv][k] - m) * kLog2eF);
+                den += e[vv];
+                num = fmaf(s[vv][k], e[vv], num);
+              }
+              const float inv = fast_rcp(den);
+              const float o1 = 1.f - num * inv;  // 1 - out
+              const float gi = go[k] * inv;
+#pragma unroll
+              for (int vv = 0; vv < kViewChunk; ++vv) d[vv][k] = gi * e[vv] * (o1 + s[vv][k]);
+            } else {
+#pragma unroll
+              for (int vv = 0; vv < kViewChunk; ++vv) d[vv][k] = (vv == am) ? go[k] : 0.f;
+            }
+          }
+#pragma unroll
+          for (int vv = 0; vv < kViewChunk; ++vv)
+            if (vv < nv && offs[vv] >= 0)
+              scatter4(c.gb + (size_t)(v0 + vv) * c.viewStride, offs[vv], s_w[warp][vv][slot], a.Cp, c.rowStride, d[vv]);
+        }
       }
-    }
 
-    if (AGG == kAggConf && a.gconf_part != nullptr) {
-      // reduce d conf over the G lane groups of the warp, then one reduction per (view, channel) per warp
-      // into one of kConfSlots partial buffers (summed by k_conf_reduce).
-#pragma unroll
-      for (int vv = 0; vv < kViewChunk; ++vv)
-#pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          float v = gcw[vv][k];
-#pragma unroll
-          for (int o = LPV; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-          gcw[vv][k] = v;
-        }
-      if (g == 0) {
-        const int slot = (T.tile_lin * kWarpsPerCta + warp) % kConfSlots;
-        float* dst = a.gconf_part + (((size_t)T.b * kConfSlots + slot) * a.V + v0) * a.C;
+      if (AGG == kAggConf && a.gconf_part != nullptr) {
+        // reduce d conf over the G lane groups of the warp, then one reduction per (view, channel) per warp
+        // into one of kConfSlots partial buffers (summed by k_conf_reduce).
 #pragma unroll
         for (int vv = 0; vv < kViewChunk; ++vv)
-          if (vv < nv)
 #pragma unroll
-            for (int k = 0; k < kCPL; ++k)
-              if (c_lane + k < a.C) atomicAdd(dst + (size_t)vv * a.C + c_lane + k, gcw[vv][k]);
+          for (int k = 0; k < kCPL; ++k) {
+            float v = gcw[vv][k];
+#pragma unroll
+            for (int o = LPV; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            gcw[vv][k] = v;
+          }
+        if (g == 0) {
+          const int slot = (T.lin * kWarpsPerCta + warp) % kConfSlots;
+          float* dst = a.gconf_part + (((size_t)T.b * kConfSlots + slot) * a.V + v0) * a.C;
+#pragma unroll
+          for (int vv = 0; vv < kViewChunk; ++vv)
+            if (vv < nv)
+#pragma unroll
+              for (int k = 0; k < kCPL; ++k)
+                if (c.c_lane + k < a.C) atomicAdd(dst + (size_t)vv * a.C + c.c_lane + k, gcw[vv][k]);
+        }
       }
     }
+    __syncwarp();  // s_go of this round is dead before the next round overwrites it (lane-private, but keep order)
   }
 }
 
 // softmax / max over MORE than kViewChunk views: per z step, pass 1 = running (max, argmax, sum e, sum e*s)
 // over all views, pass 2 = recompute each view's sample and scatter its share.
 template <int LPV, int AGG, bool ALIGNED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 1) k_unproject_bwd_manyviews(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyviews(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int SLOTS = TG::kSlots;
-  __shared__ float4 s_proj[kMaxViewsSmem * 3];
-  __shared__ float4 s_w[kWarpsPerCta][kViewChunk][SLOTS];
-  __shared__ int s_off[kWarpsPerCta][kViewChunk][SLOTS];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float4* s_proj = reinterpret_cast<float4*>(smem_raw);
+  auto s_w = reinterpret_cast<float4(*)[kViewChunk][SLOTS]>(s_proj + kMaxViewsSmem * 3);
+  auto s_go = reinterpret_cast<float4(*)[kRun][32]>(&s_w[kWarpsPerCta][0][0]);
+  auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = lane / LPV, q = lane % LPV;
-  const BwdTile T = decode_tile<LPV>(a, warp, g);
-  for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
-    s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
-  __syncthreads();
+  const TileId T = decode_tile(a);
+  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj);
+  const int warp = c.warp, lane = c.lane, g = c.g;
 
-  const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
-  const int rowStride = a.W * a.Cp;
-  const size_t viewStride = (size_t)a.H * a.W * a.Cp;
-  const size_t lane_choff = (size_t)T.cb * (LPV * kCPL) + q * kCPL;
-  const float* fb = a.feat + (size_t)T.b * a.V * viewStride + lane_choff;
-  float* gb = a.gfeat + (size_t)T.b * a.V * viewStride + lane_choff;
-  const int c_lane = (int)lane_choff;
-  const float* gp = a.gout + (size_t)T.b * a.C * a.nvox + T.run_base;
-
-  for (int j = 0; j < kRun; ++j) {
-    float go[kCPL];
+#pragma unroll 1
+  for (int r = 0; r < TG::R; ++r) {
+    const int i0 = c.i0_warp + TG::run0(r, g), i1 = c.i1_warp + TG::run1(r, g);
+    const bool run_ok = (i0 < a.N0) && (i1 < a.N1);
+    stage_grad_out<ALIGNED>(a, T.b, c.c_lane, i0, i1, c.z0, run_ok, s_go[warp], lane);
+#pragma unroll 1
+    for (int j = 0; j < kRun; ++j) {
+      const float4 gj = s_go[warp][j][lane];
+      const float go[kCPL] = {gj.x, gj.y, gj.z, gj.w};
+      float m[kCPL], se[kCPL], sw[kCPL];
+      int am[kCPL];
 #pragma unroll
-    for (int k = 0; k < kCPL; ++k) {
-      const int c = c_lane + k;
-      go[k] = (T.run_ok && c < a.C && T.z0 + j < a.N2) ? __ldg(gp + (size_t)c * a.nvox + j) : 0.f;
-    }
-    float m[kCPL], se[kCPL], sw[kCPL];
-    int am[kCPL];
-#pragma unroll
-    for (int k = 0; k < kCPL; ++k) { m[k] = -INFINITY; se[k] = 0.f; sw[k] = 0.f; am[k] = 0; }
-    // pass 1
-    for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
-      const int nv = min(kViewChunk, a.V - v0);
-      __syncwarp();
-      build_descs<LPV>(a, T, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane, invH, invW);
-      __syncwarp();
-      for (int vv = 0; vv < nv; ++vv) {
-        float s[kCPL];
-#pragma unroll
-        for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
-        const int off = s_off[warp][vv][g];
-        if (off >= 0) gather8(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][g], a.Cp, rowStride, s);
-#pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          if (s[k] > m[k]) am[k] = v0 + vv;
-          const float mn = fmaxf(m[k], s[k]);
-          if (AGG == kAggSoftmax) {
-            const float r = expf(m[k] - mn), e = expf(s[k] - mn);
-            se[k] = fmaf(se[k], r, e);
-            sw[k] = fmaf(sw[k], r, e * s[k]);
-          }
-          m[k] = mn;
-        }
-      }
-    }
-    float outv[kCPL], inv[kCPL];
-#pragma unroll
-    for (int k = 0; k < kCPL; ++k) {
-      inv[k] = (AGG == kAggSoftmax) ? __fdiv_rn(1.f, se[k]) : 0.f;
-      outv[k] = sw[k] * inv[k];
-    }
-    // pass 2
-    for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
-      const int nv = min(kViewChunk, a.V - v0);
-      __syncwarp();
-      build_descs<LPV>(a, T, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane, invH, invW);
-      __syncwarp();
-      for (int vv = 0; vv < nv; ++vv) {
-        const int off = s_off[warp][vv][g];
-        if (off < 0) continue;
-        const float4 w = s_w[warp][vv][g];
-        float d[kCPL];
-        if (AGG == kAggSoftmax) {
+      for (int k = 0; k < kCPL; ++k) { m[k] = -INFINITY; se[k] = 0.f; sw[k] = 0.f; am[k] = 0; }
+      // pass 1
+      for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
+        const int nv = min(kViewChunk, a.V - v0);
+        __syncwarp();
+        build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
+                         c.invH, c.invW);
+        __syncwarp();
+        for (int vv = 0; vv < nv; ++vv) {
           float s[kCPL];
-          gather8(fb + (size_t)(v0 + vv) * viewStride, off, w, a.Cp, rowStride, s);
 #pragma unroll
-          for (int k = 0; k < kCPL; ++k) d[k] = go[k] * (expf(s[k] - m[k]) * inv[k]) * (1.f + s[k] - outv[k]);
-        } else {
-          bool any = false;
+          for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
+          const int off = s_off[warp][vv][g];
+          if (off >= 0) gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, off, s_w[warp][vv][g], a.Cp, c.rowStride, s);
 #pragma unroll
           for (int k = 0; k < kCPL; ++k) {
-            d[k] = (am[k] == v0 + vv) ? go[k] : 0.f;
-            any |= (am[k] == v0 + vv);
+            if (s[k] > m[k]) am[k] = v0 + vv;
+            const float mn = fmaxf(m[k], s[k]);
+            if (AGG == kAggSoftmax) {
+              const float rs = fast_ex2((m[k] - mn) * kLog2eF), e = fast_ex2((s[k] - mn) * kLog2eF);
+              se[k] = fmaf(se[k], rs, e);
+              sw[k] = fmaf(sw[k], rs, e * s[k]);
+            }
+            m[k] = mn;
           }
-          if (!any) continue;
         }
-        scatter8(gb + (size_t)(v0 + vv) * viewStride, off, w, a.Cp, rowStride, d);
+      }
+      float o1[kCPL], gi[kCPL];
+#pragma unroll
+      for (int k = 0; k < kCPL; ++k) {
+        const float inv = (AGG == kAggSoftmax) ? fast_rcp(se[k]) : 0.f;
+        o1[k] = 1.f - sw[k] * inv;
+        gi[k] = go[k] * inv;
+      }
+      // pass 2
+      for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
+        const int nv = min(kViewChunk, a.V - v0);
+        __syncwarp();
+        build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
+                         c.invH, c.invW);
+        __syncwarp();
+        for (int vv = 0; vv < nv; ++vv) {
+          const int off = s_off[warp][vv][g];
+          if (off < 0) continue;
+          const float4 w = s_w[warp][vv][g];
+          float d[kCPL];
+          if (AGG == kAggSoftmax) {
+            float s[kCPL];
+            gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, s);
+#pragma unroll
+            for (int k = 0; k < kCPL; ++k) d[k] = gi[k] * fast_ex2((s[k] - m[k]) * kLog2eF) * (o1[k] + s[k]);
+          } else {
+            bool any = false;
+#pragma unroll
+            for (int k = 0; k < kCPL; ++k) {
+              d[k] = (am[k] == v0 + vv) ? go[k] : 0.f;
+              any |= (am[k] == v0 + vv);
+            }
+            if (!any) continue;
+          }
+          scatter4(c.gb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, d);
+        }
       }
     }
+    __syncwarp();
   }
 }
 
@@ -409,10 +346,18 @@ template <int LPV>
 static cudaError_t launch_bwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
   const bool aligned = (a.N2 % kRun) == 0;
   const dim3 block(kWarpsPerCta * 32);
-#define LT_LAUNCH(K, AGG_)                                      \
-  do {                                                          \
-    if (aligned) K<LPV, AGG_, true><<<grid, block, 0, st>>>(a); \
-    else K<LPV, AGG_, false><<<grid, block, 0, st>>>(a);        \
+  constexpr int SL = TileGeom<LPV>::kSlots;
+  constexpr size_t smem = sizeof(float4) * kMaxViewsSmem * 3 + kWarpsPerCta * kViewChunk * SL * (sizeof(float4) + sizeof(int)) +
+                          sizeof(float4) * kWarpsPerCta * kRun * 32;
+#define LT_LAUNCH(K, AGG_)                                                                              \
+  do {                                                                                                  \
+    if (aligned) {                                                                                      \
+      cudaFuncSetAttribute(K<LPV, AGG_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
+      K<LPV, AGG_, true><<<grid, block, smem, st>>>(a);                                                 \
+    } else {                                                                                            \
+      cudaFuncSetAttribute(K<LPV, AGG_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+      K<LPV, AGG_, false><<<grid, block, smem, st>>>(a);                                                \
+    }                                                                                                   \
   } while (0)
   switch (agg) {
     case kAggSum: LT_LAUNCH(k_unproject_bwd, kAggSum); break;
@@ -464,7 +409,6 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
   dim3 grid((unsigned)nblk);
   cudaError_t e = cudaErrorInvalidValue;
   switch (lpv) {
-    case 4: e = launch_bwd_lpv<4>(a, s.agg, grid, st); break;
     case 8: e = launch_bwd_lpv<8>(a, s.agg, grid, st); break;
     case 16: e = launch_bwd_lpv<16>(a, s.agg, grid, st); break;
     case 32: e = launch_bwd_lpv<32>(a, s.agg, grid, st); break;

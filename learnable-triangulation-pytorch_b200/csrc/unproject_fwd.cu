@@ -7,287 +7,234 @@
 
 namespace lt {
 
-// per-lane gather of one tap set: 4 x LDG.E.256 (8 channels each) and the bilinear blend, accumulated
-// in the nw, ne, sw, se order of ATen's grid_sampler_2d.
-__device__ __forceinline__ void sample8(const float* __restrict__ fv, int off, const float4& w, int Cp,
-                                        int rowStride, float (&s)[kCPL]) {
-  const float* p = fv + (off & kOffMask);
-  const int dx = (off & kOffDx) ? Cp : 0;
-  const int dy = (off & kOffDy) ? rowStride : 0;
-  f8 t00 = ldg256_nc(p);
-  f8 t01 = ldg256_nc(p + dx);
-  f8 t10 = ldg256_nc(p + dy);
-  f8 t11 = ldg256_nc(p + dy + dx);
-#pragma unroll
-  for (int k = 0; k < kCPL; ++k) {
-    float a = t00.v[k] * w.x;
-    a = fmaf(t01.v[k], w.y, a);
-    a = fmaf(t10.v[k], w.z, a);
-    a = fmaf(t11.v[k], w.w, a);
-    s[k] = a;
-  }
+// softmax over <= 4 views of one channel of one voxel: out = sum_v s_v e^{s_v} / sum_v e^{s_v}.
+// The sum is symmetric in the views, so the maximum is moved to the front with a 3-comparator network and its
+// exponential (exactly 1) is never evaluated: 3 MUFU.EX2 + 1 MUFU.RCP per channel (the SFU is the scarce pipe
+// of this kernel: round 1 ran it at 97 % with expf + IEEE divisions). Absent views carry kNoView (e -> 0).
+// ex2.approx / rcp.approx are good to ~2 ulp, far inside the 1e-5 bar.
+__device__ __forceinline__ float softmax_mix4(float s0, float s1, float s2, float s3) {
+  const float hi1 = fmaxf(s0, s1), lo1 = fminf(s0, s1), hi2 = fmaxf(s2, s3), lo2 = fminf(s2, s3);
+  const float top = fmaxf(hi1, hi2), mid = fminf(hi1, hi2);
+  const float e1 = fast_ex2((lo1 - top) * kLog2eF);
+  const float e2 = fast_ex2((lo2 - top) * kLog2eF);
+  const float e3 = fast_ex2((mid - top) * kLog2eF);
+  const float den = ((1.f + e1) + e2) + e3;
+  float num = fmaf(lo1, e1, top);
+  num = fmaf(lo2, e2, num);
+  num = fmaf(mid, e3, num);
+  return num * fast_rcp(den);
 }
 
 // AGG: lt_agg.  ALIGNED: N2 % 8 == 0 so every run is a whole, 32-byte aligned sector.
-// kAggSoftmax is only launched here for V <= kViewChunk (exact two-pass softmax in registers); more
-// views go to k_unproject_fwd_softmax_manyviews below.
+// kAggSoftmax is only launched here for V <= kViewChunk (all samples of a voxel in registers); more views go to
+// k_unproject_fwd_softmax_manyviews below.
 template <int LPV, int AGG, bool ALIGNED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_fwd(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
 
+  // dynamic smem (> 48 KB): projection rows | tap weights | tap offsets | per-lane result slots (4 ch x 8 z steps)
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float4* s_proj = reinterpret_cast<float4*>(smem_raw);
+  auto s_w = reinterpret_cast<float4(*)[kViewChunk][SLOTS]>(s_proj + kMaxViewsSmem * 3);
+  auto s_acc = reinterpret_cast<float4(*)[kRun][32]>(&s_w[kWarpsPerCta][0][0]);
+  auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_acc[kWarpsPerCta][0][0]);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane / LPV, q = lane % LPV;
+  const TileId T = decode_tile(a);
+
+  for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
+    s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
+  __syncthreads();
+
+  const int i0_warp = T.t0 * kTile0 + (warp >> 1) * kWarpRuns0;
+  const int i1_warp = T.t1 * kTile1 + (warp & 1) * kWarpRuns1;
+  const int z0 = T.t2 * kRun;
+  const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
+  const int rowStride = a.W * a.Cp;
+  const size_t viewStride = (size_t)a.H * a.W * a.Cp;
+  const int c_lane = T.cb * (LPV * kCPL) + q * kCPL;  // first channel of this lane
+  const float* fb = a.feat + (size_t)T.b * a.V * viewStride + c_lane;
+
+#pragma unroll 1
+  for (int r = 0; r < TG::R; ++r) {
+    const int i0 = i0_warp + TG::run0(r, g), i1 = i1_warp + TG::run1(r, g);
+    const bool run_ok = (i0 < a.N0) && (i1 < a.N1);
+
+#pragma unroll 1
+    for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
+      const int nv = min(kViewChunk, a.V - v0);
+      __syncwarp();
+      build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane, invH, invW);
+      __syncwarp();
+
+      float cw[kViewChunk][kCPL];
+      if (AGG == kAggConf) {
+#pragma unroll
+        for (int vv = 0; vv < kViewChunk; ++vv)
+#pragma unroll
+          for (int k = 0; k < kCPL; ++k) {
+            const int c = c_lane + k;
+            cw[vv][k] = (vv < nv && c < a.C) ? __ldg(a.conf + ((size_t)T.b * a.V + v0 + vv) * a.C + c) : 0.f;
+          }
+      }
+
+      // z loop kept ROLLED (x2): with the 8 steps unrolled ptxas hoists every descriptor and tap load of the run
+      // (~280 live registers, 600 B of spills at the 128 cap) and the SASS grows past the instruction cache.
+      // The per-step results wait in this lane's private smem slots instead of 32 accumulator registers.
+#pragma unroll 2
+      for (int j = 0; j < kRun; ++j) {
+        const int slot = j * G + g;
+        float val[kCPL];
+        if (AGG == kAggSoftmax) {
+          float s[kViewChunk][kCPL];
+#pragma unroll
+          for (int vv = 0; vv < kViewChunk; ++vv) {
+            const float fill = (vv < nv) ? 0.f : kNoView;  // zeroed views take part with 0, absent ones not at all
+#pragma unroll
+            for (int k = 0; k < kCPL; ++k) s[vv][k] = fill;
+            if (vv < nv) {
+              const int off = s_off[warp][vv][slot];
+              if (off >= 0)
+                gather4(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][slot], a.Cp, rowStride, s[vv]);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < kCPL; ++k) val[k] = softmax_mix4(s[0][k], s[1][k], s[2][k], s[3][k]);
+        } else {
+          if (v0 == 0) {
+#pragma unroll
+            for (int k = 0; k < kCPL; ++k) val[k] = (AGG == kAggMax) ? -INFINITY : 0.f;
+          } else {
+            const float4 p = s_acc[warp][j][lane];
+            val[0] = p.x; val[1] = p.y; val[2] = p.z; val[3] = p.w;
+          }
+#pragma unroll
+          for (int vv = 0; vv < kViewChunk; ++vv) {
+            if (vv < nv) {
+              float s[kCPL];
+#pragma unroll
+              for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
+              const int off = s_off[warp][vv][slot];
+              if (off >= 0) gather4(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][slot], a.Cp, rowStride, s);
+#pragma unroll
+              for (int k = 0; k < kCPL; ++k) {
+                if (AGG == kAggSum) val[k] += s[k];
+                else if (AGG == kAggConf) val[k] = fmaf(cw[vv][k], s[k], val[k]);
+                else val[k] = fmaxf(val[k], s[k]);  // MAX: zeroed views take part with 0
+              }
+            }
+          }
+        }
+        s_acc[warp][j][lane] = make_float4(val[0], val[1], val[2], val[3]);
+      }
+    }
+
+    // ---------------- store: one 32-byte sector per (channel, run) ----------------
+    if (run_ok) {
+      float acc[kCPL][kRun];
+#pragma unroll
+      for (int j = 0; j < kRun; ++j) {
+        const float4 p = s_acc[warp][j][lane];
+        acc[0][j] = p.x; acc[1][j] = p.y; acc[2][j] = p.z; acc[3][j] = p.w;
+      }
+      float* ob = a.out + (size_t)T.b * a.C * a.nvox + ((long long)i0 * a.N1 + i1) * a.N2 + z0;
+#pragma unroll
+      for (int k = 0; k < kCPL; ++k) {
+        const int c = c_lane + k;
+        if (c < a.C) {
+          float* p = ob + (size_t)c * a.nvox;
+          if (ALIGNED) {
+            stg256(p, acc[k]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < kRun; ++j)
+              if (z0 + j < a.N2) p[j] = acc[k][j];
+          }
+        }
+      }
+    }
+  }
+}
+
+// softmax over MORE than kViewChunk views: running (m, sum e, sum e*s) per channel; z step outermost so the state
+// stays at 3 x 4 registers and phase A covers G voxels x nv views per round. Same tiling, same descriptors.
+template <int LPV, bool ALIGNED>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_manyviews(const UnprojArgs a) {
+  using TG = TileGeom<LPV>;
+  constexpr int SLOTS = TG::kSlots;
   __shared__ float4 s_proj[kMaxViewsSmem * 3];
   __shared__ float4 s_w[kWarpsPerCta][kViewChunk][SLOTS];
   __shared__ int s_off[kWarpsPerCta][kViewChunk][SLOTS];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane / LPV, q = lane % LPV;
-
-  // tile decode: blockIdx.x = ((b*ncb + cb)*nt0 + t0)*nt1*nt2 + t1*nt2 + t2
-  int t = blockIdx.x;
-  const int t2 = t % a.nt2; t /= a.nt2;
-  const int t1 = t % a.nt1; t /= a.nt1;
-  const int t0 = t % a.nt0; t /= a.nt0;
-  const int cb = t % a.ncb;
-  const int b = t / a.ncb;
-
-  // projection matrices of this batch item -> smem (rows as float4)
+  const TileId T = decode_tile(a);
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
-    s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)b * a.V * 3 + i);
+    s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
   __syncthreads();
 
-  const int w0 = warp >> 1, w1 = warp & 1;
-  const int i0_warp = t0 * TG::T0 + w0 * TG::G0;
-  const int i1_warp = t1 * TG::T1 + w1 * TG::G1;
-  const int z0 = t2 * kRun;
-  // this lane group's run
-  const int i0 = i0_warp + g / TG::G1, i1 = i1_warp + g % TG::G1;
-  const bool run_ok = (i0 < a.N0) && (i1 < a.N1);
-  const long long run_base = ((long long)i0 * a.N1 + i1) * a.N2 + z0;
-
+  const int i0_warp = T.t0 * kTile0 + (warp >> 1) * kWarpRuns0;
+  const int i1_warp = T.t1 * kTile1 + (warp & 1) * kWarpRuns1;
+  const int z0 = T.t2 * kRun;
   const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
   const int rowStride = a.W * a.Cp;
   const size_t viewStride = (size_t)a.H * a.W * a.Cp;
-  const float* fb = a.feat + (size_t)b * a.V * viewStride + (size_t)cb * (LPV * kCPL) + q * kCPL;
-  const float* coord_b = a.coord + (size_t)b * a.nvox * 3;
-  const int c_lane = cb * (LPV * kCPL) + q * kCPL;  // first channel of this lane
+  const int c_lane = T.cb * (LPV * kCPL) + q * kCPL;
+  const float* fb = a.feat + (size_t)T.b * a.V * viewStride + c_lane;
 
-  float acc[kCPL][kRun];
-#pragma unroll
-  for (int k = 0; k < kCPL; ++k)
-#pragma unroll
-    for (int j = 0; j < kRun; ++j) acc[k][j] = (AGG == kAggMax) ? -INFINITY : 0.f;
-
-  for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
-    const int nv = min(kViewChunk, a.V - v0);
-    // ---------------- phase A: descriptors for SLOTS voxels x nv views ----------------
-    __syncwarp();
-    for (int slot = lane; slot < SLOTS; slot += 32) {
-      const int j = slot / G, gg = slot % G;
-      const int vi0 = i0_warp + gg / TG::G1, vi1 = i1_warp + gg % TG::G1, vz = z0 + j;
-      const bool ok = (vi0 < a.N0) && (vi1 < a.N1) && (vz < a.N2);
-      float x = 0.f, y = 0.f, z = 0.f;
-      if (ok) {
-        const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
-        x = __ldg(cp); y = __ldg(cp + 1); z = __ldg(cp + 2);
-      }
-      for (int vv = 0; vv < nv; ++vv) {
-        int off = -1;
-        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (ok) {
-          const int v = v0 + vv;
-          float4 r0, r1, r2;
-          if (v < kMaxViewsSmem) {
-            r0 = s_proj[v * 3]; r1 = s_proj[v * 3 + 1]; r2 = s_proj[v * 3 + 2];
-          } else {
-            const float4* pp = reinterpret_cast<const float4*>(a.proj) + ((size_t)b * a.V + v) * 3;
-            r0 = __ldg(pp); r1 = __ldg(pp + 1); r2 = __ldg(pp + 2);
-          }
-          make_desc(x, y, z, r0, r1, r2, a.H, a.W, a.Cp, invH, invW, a.align_corners, off, w);
-        }
-        s_w[warp][vv][slot] = w;
-        s_off[warp][vv][slot] = off;
-      }
-    }
-    __syncwarp();
-
-    // ---------------- phase B: gather + aggregate ----------------
-    float cw[kViewChunk][kCPL];
-    if (AGG == kAggConf) {
-#pragma unroll
-      for (int vv = 0; vv < kViewChunk; ++vv)
-#pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          const int c = c_lane + k;
-          cw[vv][k] = (vv < nv && c < a.C) ? __ldg(a.conf + ((size_t)b * a.V + v0 + vv) * a.C + c) : 0.f;
-        }
-    }
-
+#pragma unroll 1
+  for (int r = 0; r < TG::R; ++r) {
+    const int i0 = i0_warp + TG::run0(r, g), i1 = i1_warp + TG::run1(r, g);
+    const bool run_ok = (i0 < a.N0) && (i1 < a.N1);
+    float res[kCPL][kRun];
 #pragma unroll
     for (int j = 0; j < kRun; ++j) {
-      const int slot = j * G + g;
-      if (AGG == kAggSoftmax) {
-        // exact two-pass softmax over the (<= kViewChunk) views of this chunk
-        float s[kViewChunk][kCPL];
+      float m[kCPL], se[kCPL], sw[kCPL];
 #pragma unroll
-        for (int vv = 0; vv < kViewChunk; ++vv) {
+      for (int k = 0; k < kCPL; ++k) { m[k] = -INFINITY; se[k] = 0.f; sw[k] = 0.f; }
+#pragma unroll 1
+      for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
+        const int nv = min(kViewChunk, a.V - v0);
+        __syncwarp();
+        build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane, invH, invW);
+        __syncwarp();
+        for (int vv = 0; vv < nv; ++vv) {
+          float s[kCPL];
 #pragma unroll
-          for (int k = 0; k < kCPL; ++k) s[vv][k] = 0.f;
-          if (vv < nv) {
-            const int off = s_off[warp][vv][slot];
-            if (off >= 0) sample8(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][slot], a.Cp, rowStride, s[vv]);
-          }
-        }
+          for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
+          const int off = s_off[warp][vv][g];
+          if (off >= 0) gather4(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][g], a.Cp, rowStride, s);
 #pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          float m = s[0][k];
-#pragma unroll
-          for (int vv = 1; vv < kViewChunk; ++vv)
-            if (vv < nv) m = fmaxf(m, s[vv][k]);
-          float e[kViewChunk], den = 0.f;
-#pragma unroll
-          for (int vv = 0; vv < kViewChunk; ++vv) {
-            e[vv] = (vv < nv) ? expf(s[vv][k] - m) : 0.f;
-            den += e[vv];
-          }
-          float o = 0.f;
-#pragma unroll
-          for (int vv = 0; vv < kViewChunk; ++vv)
-            if (vv < nv) o = fmaf(s[vv][k], __fdiv_rn(e[vv], den), o);
-          acc[k][j] = o;
-        }
-      } else {
-#pragma unroll
-        for (int vv = 0; vv < kViewChunk; ++vv) {
-          if (vv < nv) {
-            float s[kCPL];
-#pragma unroll
-            for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
-            const int off = s_off[warp][vv][slot];
-            if (off >= 0) sample8(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][slot], a.Cp, rowStride, s);
-#pragma unroll
-            for (int k = 0; k < kCPL; ++k) {
-              if (AGG == kAggSum) acc[k][j] += s[k];
-              else if (AGG == kAggConf) acc[k][j] = fmaf(cw[vv][k], s[k], acc[k][j]);
-              else acc[k][j] = fmaxf(acc[k][j], s[k]);  // MAX: zeroed views take part with 0
-            }
+          for (int k = 0; k < kCPL; ++k) {
+            const float mn = fmaxf(m[k], s[k]);
+            const float rs = fast_ex2((m[k] - mn) * kLog2eF), e = fast_ex2((s[k] - mn) * kLog2eF);  // ex2(-inf) = 0
+            se[k] = fmaf(se[k], rs, e);
+            sw[k] = fmaf(sw[k], rs, e * s[k]);
+            m[k] = mn;
           }
         }
       }
+#pragma unroll
+      for (int k = 0; k < kCPL; ++k) res[k][j] = sw[k] * fast_rcp(se[k]);
     }
-  }
-
-  // ---------------- store: one 32-byte sector per (channel, run) ----------------
-  if (!run_ok) return;
-  float* ob = a.out + (size_t)b * a.C * a.nvox + run_base;
+    if (run_ok) {
+      float* ob = a.out + (size_t)T.b * a.C * a.nvox + ((long long)i0 * a.N1 + i1) * a.N2 + z0;
 #pragma unroll
-  for (int k = 0; k < kCPL; ++k) {
-    const int c = c_lane + k;
-    if (c < a.C) {
-      float* p = ob + (size_t)c * a.nvox;
-      if (ALIGNED) {
-        stg256(p, acc[k]);
-      } else {
+      for (int k = 0; k < kCPL; ++k) {
+        const int c = c_lane + k;
+        if (c < a.C) {
+          float* p = ob + (size_t)c * a.nvox;
+          if (ALIGNED) {
+            stg256(p, res[k]);
+          } else {
 #pragma unroll
-        for (int j = 0; j < kRun; ++j)
-          if (z0 + j < a.N2) p[j] = acc[k][j];
-      }
-    }
-  }
-}
-
-// softmax over MORE than kViewChunk views: running (m, sum e, sum e*s) per channel; one z step at a time
-// so that the state stays at 3*8 registers. Same tiling, same descriptors.
-template <int LPV, bool ALIGNED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_manyviews(const UnprojArgs a) {
-  using TG = TileGeom<LPV>;
-  constexpr int G = TG::G;
-  constexpr int SLOTS = TG::kSlots;
-  __shared__ float4 s_w[kWarpsPerCta][kViewChunk][SLOTS];
-  __shared__ int s_off[kWarpsPerCta][kViewChunk][SLOTS];
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = lane / LPV, q = lane % LPV;
-  int t = blockIdx.x;
-  const int t2 = t % a.nt2; t /= a.nt2;
-  const int t1 = t % a.nt1; t /= a.nt1;
-  const int t0 = t % a.nt0; t /= a.nt0;
-  const int cb = t % a.ncb;
-  const int b = t / a.ncb;
-  const int w0 = warp >> 1, w1 = warp & 1;
-  const int i0_warp = t0 * TG::T0 + w0 * TG::G0;
-  const int i1_warp = t1 * TG::T1 + w1 * TG::G1;
-  const int z0 = t2 * kRun;
-  const int i0 = i0_warp + g / TG::G1, i1 = i1_warp + g % TG::G1;
-  const bool run_ok = (i0 < a.N0) && (i1 < a.N1);
-  const long long run_base = ((long long)i0 * a.N1 + i1) * a.N2 + z0;
-  const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
-  const int rowStride = a.W * a.Cp;
-  const size_t viewStride = (size_t)a.H * a.W * a.Cp;
-  const float* fb = a.feat + (size_t)b * a.V * viewStride + (size_t)cb * (LPV * kCPL) + q * kCPL;
-  const float* coord_b = a.coord + (size_t)b * a.nvox * 3;
-  const int c_lane = cb * (LPV * kCPL) + q * kCPL;
-
-  // z step outermost: the running state is 3 x 8 registers and phase A covers G voxels x nv views.
-  float res[kCPL][kRun];
-#pragma unroll
-  for (int j = 0; j < kRun; ++j) {
-    float m[kCPL], se[kCPL], sw[kCPL];
-#pragma unroll
-    for (int k = 0; k < kCPL; ++k) { m[k] = -INFINITY; se[k] = 0.f; sw[k] = 0.f; }
-    for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
-      const int nv = min(kViewChunk, a.V - v0);
-      __syncwarp();
-      // phase A restricted to z step j: G voxels x nv views, one descriptor per lane at most
-      for (int d = lane; d < G * nv; d += 32) {
-        const int gg = d % G, vv = d / G;
-        const int vi0 = i0_warp + gg / TG::G1, vi1 = i1_warp + gg % TG::G1, vz = z0 + j;
-        int off = -1;
-        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-        if ((vi0 < a.N0) && (vi1 < a.N1) && (vz < a.N2)) {
-          const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
-          const float4* pp = reinterpret_cast<const float4*>(a.proj) + ((size_t)b * a.V + v0 + vv) * 3;
-          make_desc(__ldg(cp), __ldg(cp + 1), __ldg(cp + 2), __ldg(pp), __ldg(pp + 1), __ldg(pp + 2), a.H, a.W,
-                    a.Cp, invH, invW, a.align_corners, off, w);
+            for (int j = 0; j < kRun; ++j)
+              if (z0 + j < a.N2) p[j] = res[k][j];
+          }
         }
-        s_w[warp][vv][gg] = w;
-        s_off[warp][vv][gg] = off;
-      }
-      __syncwarp();
-      for (int vv = 0; vv < nv; ++vv) {
-        float s[kCPL];
-#pragma unroll
-        for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
-        const int off = s_off[warp][vv][g];
-        if (off >= 0) sample8(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][g], a.Cp, rowStride, s);
-#pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          const float mn = fmaxf(m[k], s[k]);
-          const float r = expf(m[k] - mn), e = expf(s[k] - mn);  // expf(-inf)=0 on the first view
-          se[k] = fmaf(se[k], r, e);
-          sw[k] = fmaf(sw[k], r, e * s[k]);
-          m[k] = mn;
-        }
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < kCPL; ++k) res[k][j] = __fdiv_rn(sw[k], se[k]);
-  }
-
-  if (!run_ok) return;
-  float* ob = a.out + (size_t)b * a.C * a.nvox + run_base;
-#pragma unroll
-  for (int k = 0; k < kCPL; ++k) {
-    const int c = c_lane + k;
-    if (c < a.C) {
-      float* p = ob + (size_t)c * a.nvox;
-      if (ALIGNED) {
-        stg256(p, res[k]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < kRun; ++j)
-          if (z0 + j < a.N2) p[j] = res[k][j];
       }
     }
   }
@@ -297,10 +244,18 @@ template <int LPV>
 static cudaError_t launch_fwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
   const bool aligned = (a.N2 % kRun) == 0;
   const dim3 block(kWarpsPerCta * 32);
-#define LT_LAUNCH(AGG_)                                                      \
-  do {                                                                       \
-    if (aligned) k_unproject_fwd<LPV, AGG_, true><<<grid, block, 0, st>>>(a); \
-    else k_unproject_fwd<LPV, AGG_, false><<<grid, block, 0, st>>>(a);        \
+  constexpr int SL = TileGeom<LPV>::kSlots;
+  constexpr size_t smem = sizeof(float4) * kMaxViewsSmem * 3 + kWarpsPerCta * kViewChunk * SL * (sizeof(float4) + sizeof(int)) +
+                          sizeof(float4) * kWarpsPerCta * kRun * 32;
+#define LT_LAUNCH(AGG_)                                                                                    \
+  do {                                                                                                     \
+    if (aligned) {                                                                                         \
+      cudaFuncSetAttribute(k_unproject_fwd<LPV, AGG_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
+      k_unproject_fwd<LPV, AGG_, true><<<grid, block, smem, st>>>(a);                                      \
+    } else {                                                                                               \
+      cudaFuncSetAttribute(k_unproject_fwd<LPV, AGG_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+      k_unproject_fwd<LPV, AGG_, false><<<grid, block, smem, st>>>(a);                                     \
+    }                                                                                                      \
   } while (0)
   switch (agg) {
     case kAggSum: LT_LAUNCH(kAggSum); break;
@@ -318,16 +273,13 @@ static cudaError_t launch_fwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaS
 }
 
 void fill_unproj_tiling(UnprojArgs& a, int lpv) {
-  const int G = 32 / lpv;
-  const int G1 = G < 4 ? G : 4, G0 = G / G1;
-  const int T0 = 4 * G0, T1 = 2 * G1;
-  a.nt0 = (a.N0 + T0 - 1) / T0;
-  a.nt1 = (a.N1 + T1 - 1) / T1;
+  a.nt0 = (a.N0 + kTile0 - 1) / kTile0;
+  a.nt1 = (a.N1 + kTile1 - 1) / kTile1;
   a.nt2 = (a.N2 + kRun - 1) / kRun;
   a.ncb = a.Cp / (lpv * kCPL);
 }
 
-int unproj_lpv(int Cp) { return Cp >= 256 ? 32 : Cp / kCPL; }
+int unproj_lpv(int Cp) { return Cp >= kMaxLanesPerVoxel * kCPL ? kMaxLanesPerVoxel : Cp / kCPL; }
 
 cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const float* coord,
                                  const float* conf, float* out, const UnprojShape& s, cudaStream_t st) {
@@ -343,7 +295,6 @@ cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
   dim3 grid((unsigned)nblk);
   switch (lpv) {
-    case 4: return launch_fwd_lpv<4>(a, s.agg, grid, st);
     case 8: return launch_fwd_lpv<8>(a, s.agg, grid, st);
     case 16: return launch_fwd_lpv<16>(a, s.agg, grid, st);
     case 32: return launch_fwd_lpv<32>(a, s.agg, grid, st);

@@ -40,7 +40,7 @@ def test_host_side_entry_points_without_gpu():
     L = _lib.lib()
     assert L.lt_abi_version() == 1
     assert L.lt_padded_channels(32) == 32 and L.lt_padded_channels(17) == 32
-    assert L.lt_padded_channels(33) == 64 and L.lt_padded_channels(256) == 256 and L.lt_padded_channels(300) == 512
+    assert L.lt_padded_channels(33) == 64 and L.lt_padded_channels(256) == 256 and L.lt_padded_channels(300) == 384
     assert L.lt_softargmax_ws_bytes(16, 17, 64 ** 3) == 16 * 17 * 64 * 8 * 5 * 4
     # bad arguments come back as LT_ERR_INVALID with a message, nothing is launched
     rc = L.lt_dlt_fwd(None, None, None, None, None, 1, 0, 1, None)
