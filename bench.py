@@ -129,8 +129,7 @@ class DeviceStep:
         self.N = tuple(self.coord.shape[1:4])
         nvox = self.N[0] * self.N[1] * self.N[2]
         self.nvox = nvox
-        Cp = self.L.lt_padded_channels(w["C"])
-        self.feat_hwc = torch.empty((B, w["V"], w["H"], w["W"], Cp), device=dev)
+        self.feat_hwc = torch.empty((self.L.lt_feat_layout_elems(B * w["V"], w["C"], w["H"], w["W"]),), device=dev)
         self.vol = torch.empty((B, w["C"]) + self.N, device=dev)
         gd = torch.Generator(device=dev).manual_seed(seed + 6)
         self.gvol = torch.randn((B, w["C"]) + self.N, generator=gd, device=dev)     # upstream grad of K1's output

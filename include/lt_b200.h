@@ -40,15 +40,18 @@ const char *lt_last_error(void);
 
 /* ---- K0: feature layout ------------------------------------------------------------------------
  * The reference hands (B,V,C,H,W) channel-planar maps to F.grid_sample (op.py:114-134). The gather
- * kernels want one texel = one contiguous run of channels, so K0 re-tiles to (B·V,H,W,Cp), channels
- * last, Cp = lt_padded_channels(C) >= C (zero filled). lt_feat_to_chw is the inverse, used for
- * grad_heatmaps; it drops the padding. */
+ * kernels want one tap = one contiguous run of channels, so K0 re-tiles to the library's gather
+ * layout "hwcp": (B·V, H+2, W+2, Cp) channels-last, Cp = lt_padded_channels(C) >= C (zero filled),
+ * with a one-texel ZERO border around every map (grid_sample's zeros padding as data instead of
+ * per-tap bounds logic). Callers treat it as an opaque buffer of lt_feat_layout_elems() floats.
+ * lt_feat_to_chw is the inverse, used for grad_heatmaps; it drops border and padding. */
 int lt_padded_channels(int C);
-int lt_feat_to_hwc(const float *src_chw, float *dst_hwc, int BV, int C, int H, int W, void *stream);
-int lt_feat_to_chw(const float *src_hwc, float *dst_chw, int BV, int C, int H, int W, void *stream);
+size_t lt_feat_layout_elems(int BV, int C, int H, int W);
+int lt_feat_to_hwc(const float *src_chw, float *dst_hwcp, int BV, int C, int H, int W, void *stream);
+int lt_feat_to_chw(const float *src_hwcp, float *dst_chw, int BV, int C, int H, int W, void *stream);
 
 /* ---- K1: fused unproject + view aggregation  (op.py:99-163) ------------------------------------
- * feat_hwc (B,V,H,W,Cp)   proj (B,V,3,4)   coord (B,N0,N1,N2,3)   conf (B,V,C) or NULL
+ * feat_hwc: (B*V) maps in the hwcp layout of K0   proj (B,V,3,4)   coord (B,N0,N1,N2,3)   conf (B,V,C) or NULL
  * out (B,C,N0,N1,N2).  align_corners: 0 = F.grid_sample default of torch>=1.3 (what the reference
  * runs as today), 1 = torch 1.0.1 behaviour (requirements.txt:20).
  * Semantics: p=[x y z 1]·Pᵀ; voxels with p.z<=0 contribute 0 for that view (op.py:121,138);
@@ -59,7 +62,7 @@ int lt_unproject_fwd(const float *feat_hwc, const float *proj, const float *coor
                      int agg, int align_corners, void *stream);
 
 /* Backward of the above w.r.t. heatmaps and vol_confidences (proj/coord never need grad:
- * triangulation.py:277,283). grad_feat_hwc (B,V,H,W,Cp) MUST be zero-filled by the caller: the
+ * triangulation.py:277,283). grad_feat_hwc (hwcp layout, lt_feat_layout_elems floats) MUST be zero-filled by the caller: the
  * kernel scatter-adds into it with vector reductions (non-deterministic summation order).
  * grad_conf (B,V,C) may be NULL (required non-NULL only for LT_AGG_CONF if wanted); it is
  * fully overwritten. conf_ws: scratch of lt_unproject_bwd_ws_bytes() bytes (may be NULL when

@@ -24,6 +24,7 @@ SIGNATURES = {
     "lt_abi_version": (_i, []),
     "lt_last_error": (ctypes.c_char_p, []),
     "lt_padded_channels": (_i, [_i]),
+    "lt_feat_layout_elems": (ctypes.c_size_t, [_i, _i, _i, _i]),
     "lt_feat_to_hwc": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "lt_feat_to_chw": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "lt_unproject_fwd": (_i, [_vp, _vp, _vp, _vp, _vp] + [_i] * 10 + [_vp]),

@@ -25,7 +25,7 @@ inline cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
 
 bool bad_unproj_shape(int B, int V, int C, int H, int W, int N0, int N1, int N2) {
   return B < 0 || V < 1 || C < 0 || H < 1 || W < 1 || N0 < 0 || N1 < 0 || N2 < 0 ||
-         (long long)H * W * lt::padded_channels(C > 0 ? C : 1) > 0x0fffffffLL;
+         (long long)(H + 2) * (W + 2) * lt::padded_channels(C > 0 ? C : 1) > 0x0fffffffLL;
 }
 
 }  // namespace
@@ -42,6 +42,7 @@ LT_API int lt_abi_version(void) { return LT_ABI_VERSION; }
 LT_API const char* lt_last_error(void) { return g_err; }
 
 LT_API int lt_padded_channels(int C) { return C > 0 ? lt::padded_channels(C) : 0; }
+LT_API size_t lt_feat_layout_elems(int BV, int C, int H, int W) { return lt::feat_layout_elems(BV, C, H, W); }
 
 LT_API int lt_feat_to_hwc(const float* src_chw, float* dst_hwc, int BV, int C, int H, int W, void* stream) {
   LT_REQUIRE(BV >= 0 && C >= 0 && H >= 0 && W >= 0, "negative extent");

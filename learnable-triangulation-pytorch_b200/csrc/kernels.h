@@ -8,7 +8,8 @@ namespace lt {
 constexpr int kAggSum = 0, kAggConf = 1, kAggMax = 2, kAggSoftmax = 3;  // == enum lt_agg
 
 int padded_channels(int C);
-cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwc,
+size_t feat_layout_elems(int BV, int C, int H, int W);
+cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwcp,
                                cudaStream_t st);
 
 struct UnprojShape {

@@ -21,9 +21,9 @@ constexpr int kConfSlots = 64;  // grad_conf partial-sum slots per batch item
 // scatter-add w_tap * d[0..3] into the four taps; taps with zero weight (outside the map) are skipped.
 __device__ __forceinline__ void scatter4(float* __restrict__ gv, int off, const float4& w, int Cp,
                                          int rowStride, const float (&d)[kCPL]) {
-  float* p = gv + (off & kOffMask);
-  const int dx = (off & kOffDx) ? Cp : 0;
-  const int dy = (off & kOffDy) ? rowStride : 0;
+  float* p = gv + off;
+  const int dx = Cp;
+  const int dy = rowStride;
   if (w.x != 0.f) red_add_v4(p, d[0] * w.x, d[1] * w.x, d[2] * w.x, d[3] * w.x);
   if (w.y != 0.f) red_add_v4(p + dx, d[0] * w.y, d[1] * w.y, d[2] * w.y, d[3] * w.y);
   if (w.z != 0.f) red_add_v4(p + dy, d[0] * w.z, d[1] * w.z, d[2] * w.z, d[3] * w.z);
@@ -51,8 +51,8 @@ __device__ __forceinline__ BwdCtx bwd_prologue(const UnprojArgs& a, const TileId
   c.i1_warp = T.t1 * kTile1 + (c.warp & 1) * kWarpRuns1;
   c.z0 = T.t2 * kRun;
   c.invH = 1.f / (float)a.H; c.invW = 1.f / (float)a.W;
-  c.rowStride = a.W * a.Cp;
-  c.viewStride = (size_t)a.H * a.W * a.Cp;
+  c.rowStride = (a.W + 2) * a.Cp;
+  c.viewStride = (size_t)(a.H + 2) * (a.W + 2) * a.Cp;
   c.c_lane = T.cb * (LPV * kCPL) + c.q * kCPL;
   c.fb = a.feat + (size_t)T.b * a.V * c.viewStride + c.c_lane;
   c.gb = a.gfeat + (size_t)T.b * a.V * c.viewStride + c.c_lane;

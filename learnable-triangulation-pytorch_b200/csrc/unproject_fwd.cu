@@ -53,8 +53,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_fwd(const Un
   const int i1_warp = T.t1 * kTile1 + (warp & 1) * kWarpRuns1;
   const int z0 = T.t2 * kRun;
   const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
-  const int rowStride = a.W * a.Cp;
-  const size_t viewStride = (size_t)a.H * a.W * a.Cp;
+  const int rowStride = (a.W + 2) * a.Cp;
+  const size_t viewStride = (size_t)(a.H + 2) * (a.W + 2) * a.Cp;
   const int c_lane = T.cb * (LPV * kCPL) + q * kCPL;  // first channel of this lane
   const float* fb = a.feat + (size_t)T.b * a.V * viewStride + c_lane;
 
@@ -180,8 +180,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
   const int i1_warp = T.t1 * kTile1 + (warp & 1) * kWarpRuns1;
   const int z0 = T.t2 * kRun;
   const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
-  const int rowStride = a.W * a.Cp;
-  const size_t viewStride = (size_t)a.H * a.W * a.Cp;
+  const int rowStride = (a.W + 2) * a.Cp;
+  const size_t viewStride = (size_t)(a.H + 2) * (a.W + 2) * a.Cp;
   const int c_lane = T.cb * (LPV * kCPL) + q * kCPL;
   const float* fb = a.feat + (size_t)T.b * a.V * viewStride + c_lane;
 

@@ -45,14 +45,13 @@ class _Unproject(torch.autograd.Function):
         L = _lib.lib()
         B, V, C, H, W = heatmaps.shape
         N0, N1, N2 = coord.shape[1:4]
-        Cp = L.lt_padded_channels(C) if C > 0 else 0
         with torch.cuda.device(heatmaps.device):
             st = _stream()
             hm = _f32c(heatmaps)
             proj_c, coord_c = _f32c(proj), _f32c(coord)
             conf_c = _f32c(conf) if conf is not None else None
-            # K0: channels-last, padded copy of the feature maps (one texel = one contiguous run)
-            feat = torch.empty((B, V, H, W, Cp), device=hm.device, dtype=torch.float32)
+            # K0: gather layout (16-channel groups, zero border) of the feature maps; opaque to this side
+            feat = torch.empty((L.lt_feat_layout_elems(B * V, C, H, W),), device=hm.device, dtype=torch.float32)
             _lib.check(L.lt_feat_to_hwc(_lib.ptr(hm), _lib.ptr(feat), B * V, C, H, W, st))
             out = torch.empty((B, C, N0, N1, N2), device=hm.device, dtype=torch.float32)
             _lib.check(L.lt_unproject_fwd(_lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c), _lib.ptr(conf_c),
