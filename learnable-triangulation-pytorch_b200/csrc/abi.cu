@@ -1,6 +1,7 @@
 // abi.cu — the extern "C" surface declared in include/lt_b200.h. Argument checking, error strings and
 // dispatch only; every entry point ends in a kernel launch on the caller's stream (no CPU path exists).
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/lt_b200.h"
@@ -121,6 +122,8 @@ LT_API int lt_softargmax_finalize(const float* vol, const float* stats, float* c
 
 LT_API int lt_softargmax_fwd(const float* vol, const float* coord, float* coords, float* prob, float* stats, void* ws,
                       int B, int J, long long nvox, int softmax, float multiplier, void* stream) {
+  // (Running partial+finalize per L2-sized group of batch items, so that the second read of the volumes hits L2, was
+  //  measured on B200 and is slower at every group size: the per-group launches no longer fill 148 SMs.)
   int rc = lt_softargmax_partial(vol, coord, stats, ws, B, J, nvox, softmax, multiplier, stream);
   if (rc) return rc;
   return lt_softargmax_finalize(vol, stats, coords, prob, B, J, nvox, softmax, multiplier, stream);

@@ -35,30 +35,49 @@ __global__ void __launch_bounds__(256) k_feat_layout(const float* __restrict__ s
   const size_t planar_base = ((size_t)bv * C + c0) * H * W + (size_t)(row_in ? y : 0) * W;
   const size_t hwcp_base = (((size_t)bv * Hp + yp) * Wp + xp0) * Cp + c0;
 
+  // planar side: thread -> pixel t%64, channels t/64 + 4k (coalesced 256-byte rows, no index arithmetic in the loop)
+  // hwcp side  : thread -> channel quad t%8, pixels t/8 + 32k (one 16-byte vector per thread, 128 bytes per pixel)
+  // tile[c*65 + p]: both access patterns are bank-conflict free (65 = 1 mod 32).
+  const int pp = threadIdx.x & (kPixTile - 1), pc = threadIdx.x >> 6;
+  const int hq = threadIdx.x & 7, hp = threadIdx.x >> 3;
+  const int x = xp0 + pp - 1;
+  const bool px_in = row_in && pp < npix && x >= 0 && x < W;
   if (TO_HWCP) {
-    for (int i = threadIdx.x; i < kChanTile * kPixTile; i += blockDim.x) {
-      const int c = i / kPixTile, p = i % kPixTile;
-      const int x = xp0 + p - 1;
+    const float* sp = src + planar_base + (size_t)pc * H * W + x;
+#pragma unroll
+    for (int k = 0; k < kChanTile / 4; ++k) {
+      const int c = pc + 4 * k;
       float v = 0.f;
-      if (row_in && p < npix && x >= 0 && x < W && c0 + c < C) v = __ldg(src + planar_base + (size_t)c * H * W + x);
-      tile[c * (kPixTile + 1) + p] = v;
+      if (px_in && c0 + c < C) v = __ldg(sp + (size_t)(4 * k) * H * W);
+      tile[c * (kPixTile + 1) + pp] = v;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < npix * kChanTile; i += blockDim.x) {
-      const int p = i / kChanTile, c = i % kChanTile;
-      dst[hwcp_base + (size_t)p * Cp + c] = tile[c * (kPixTile + 1) + p];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int p = hp + 32 * k;
+      if (p < npix) {
+        const float* t = tile + (4 * hq) * (kPixTile + 1) + p;
+        const float4 v = make_float4(t[0], t[kPixTile + 1], t[2 * (kPixTile + 1)], t[3 * (kPixTile + 1)]);
+        *reinterpret_cast<float4*>(dst + hwcp_base + (size_t)p * Cp + 4 * hq) = v;
+      }
     }
   } else {
     if (!row_in) return;
-    for (int i = threadIdx.x; i < npix * kChanTile; i += blockDim.x) {
-      const int p = i / kChanTile, c = i % kChanTile;
-      tile[c * (kPixTile + 1) + p] = __ldg(src + hwcp_base + (size_t)p * Cp + c);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int p = hp + 32 * k;
+      if (p < npix) {
+        const float4 v = ldg128_stream(src + hwcp_base + (size_t)p * Cp + 4 * hq);
+        float* t = tile + (4 * hq) * (kPixTile + 1) + p;
+        t[0] = v.x; t[kPixTile + 1] = v.y; t[2 * (kPixTile + 1)] = v.z; t[3 * (kPixTile + 1)] = v.w;
+      }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < kChanTile * kPixTile; i += blockDim.x) {
-      const int c = i / kPixTile, p = i % kPixTile;
-      const int x = xp0 + p - 1;
-      if (p < npix && x >= 0 && x < W && c0 + c < C) dst[planar_base + (size_t)c * H * W + x] = tile[c * (kPixTile + 1) + p];
+    float* dp = dst + planar_base + (size_t)pc * H * W + x;
+#pragma unroll
+    for (int k = 0; k < kChanTile / 4; ++k) {
+      const int c = pc + 4 * k;
+      if (px_in && c0 + c < C) dp[(size_t)(4 * k) * H * W] = tile[c * (kPixTile + 1) + pp];
     }
   }
 }

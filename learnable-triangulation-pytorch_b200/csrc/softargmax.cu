@@ -19,8 +19,8 @@
 namespace lt {
 
 constexpr int kSamThreads = 256;
-constexpr int kSamEpt = 16;                          // voxels per thread: 4 groups of 4 (float4)
-constexpr int kSamChunk = kSamThreads * kSamEpt;     // 4096 voxels per CTA
+constexpr int kSamEpt = 8;                           // voxels per thread: 2 groups of 4 (float4)
+constexpr int kSamChunk = kSamThreads * kSamEpt;     // 2048 voxels per CTA
 constexpr int kSamWarps = kSamThreads / 32;
 constexpr float kLog2e = 1.4426950408889634f;
 
@@ -36,7 +36,7 @@ static inline int sam_chunks(long long nvox) { return (int)((nvox + kSamChunk - 
 // pass 1: partial tuples. ws layout: [(b*J + j)][chunk*kSamWarps + warp][5]
 // VEC: nvox % 4 == 0 (rows 16-byte aligned) -> 128-bit loads.
 template <bool VEC, bool SOFTMAX>
-__global__ void __launch_bounds__(kSamThreads) k_sam_stats(const float* __restrict__ vol,
+__global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __restrict__ vol,
                                                            const float* __restrict__ coord,
                                                            float* __restrict__ ws, int J, long long nvox,
                                                            float mult) {
@@ -72,9 +72,9 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_stats(const float* __restri
   }
 
   const float L = mult * kLog2e;
-  for (int j = 0; j < J; ++j) {
+  // rows are double-buffered in registers: the loads of joint j+1 are in flight while joint j is reduced
+  auto load_row = [&](int j, float (&x)[kSamEpt]) {
     const float* row = vol + ((size_t)b * J + j) * nvox;
-    float x[kSamEpt];
 #pragma unroll
     for (int i = 0; i < kSamEpt / 4; ++i) {
       const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
@@ -86,6 +86,8 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_stats(const float* __restri
         for (int e = 0; e < 4; ++e) x[i * 4 + e] = (v0 + e < nvox) ? __ldg(row + v0 + e) : -INFINITY;
       }
     }
+  };
+  auto reduce_row = [&](int j, const float (&x)[kSamEpt]) {
     Lse5 r;
     if (SOFTMAX) {
       // shift by the warp-wide max of the scaled logits (mult > 0 is guaranteed by the caller); padding
@@ -121,6 +123,16 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_stats(const float* __restri
     if (lane == 0) {
       float* o = ws + (((size_t)b * J + j) * nchunk * kSamWarps + (size_t)chunk * kSamWarps + warp) * 5;
       o[0] = r.m; o[1] = r.s; o[2] = r.x; o[3] = r.y; o[4] = r.z;
+    }
+  };
+  float xa[kSamEpt], xb[kSamEpt];
+  if (J > 0) load_row(0, xa);
+  for (int j = 0; j < J; j += 2) {
+    if (j + 1 < J) load_row(j + 1, xb);
+    reduce_row(j, xa);
+    if (j + 1 < J) {
+      if (j + 2 < J) load_row(j + 2, xa);
+      reduce_row(j + 1, xb);
     }
   }
 }
@@ -161,7 +173,8 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_final(const float* __restri
                                                            const float* __restrict__ stats,
                                                            float* __restrict__ coords, float* __restrict__ prob,
                                                            long long nvox, float mult) {
-  const int bj = blockIdx.y, chunk = blockIdx.x;
+  // reverse traversal: the rows the statistics pass read LAST are the ones still in L2, so they are re-read FIRST
+  const int bj = gridDim.y - 1 - blockIdx.y, chunk = gridDim.x - 1 - blockIdx.x;
   const float* st = stats + (size_t)bj * 5;
   const float m = __ldg(st), S = __ldg(st + 1);
   const float invS = SOFTMAX ? __fdiv_rn(1.f, S) : 1.f;
@@ -236,7 +249,37 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_bwd(const float* __restrict
       }
     }
   }
-  for (int j = 0; j < J; ++j) {
+  // rows (saved probabilities and, when present, the dense upstream gradient) are double-buffered in registers:
+  // the loads of joint j+1 are in flight while joint j is computed and stored
+  auto load_rows = [&](int j, float (&p)[kSamEpt], float (&gp)[kSamEpt]) {
+    const size_t bj = (size_t)b * J + j;
+    const float* prow = prob + bj * nvox;
+    const float* grow = HAS_GP ? gprob + bj * nvox : nullptr;
+#pragma unroll
+    for (int i = 0; i < kSamEpt / 4; ++i) {
+      const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { p[i * 4 + e] = 0.f; gp[i * 4 + e] = 0.f; }
+      if (VEC) {
+        if (v0 < nvox) {
+          float4 t = ldg128_stream(prow + v0);
+          p[i * 4] = t.x; p[i * 4 + 1] = t.y; p[i * 4 + 2] = t.z; p[i * 4 + 3] = t.w;
+          if (HAS_GP) {
+            float4 u = ldg128_stream(grow + v0);
+            gp[i * 4] = u.x; gp[i * 4 + 1] = u.y; gp[i * 4 + 2] = u.z; gp[i * 4 + 3] = u.w;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (v0 + e < nvox) {
+            p[i * 4 + e] = __ldg(prow + v0 + e);
+            if (HAS_GP) gp[i * 4 + e] = __ldg(grow + v0 + e);
+          }
+      }
+    }
+  };
+  auto emit = [&](int j, const float (&p)[kSamEpt], const float (&gp)[kSamEpt]) {
     const size_t bj = (size_t)b * J + j;
     const float gx = __ldg(gcoords + bj * 3), gy = __ldg(gcoords + bj * 3 + 1), gz = __ldg(gcoords + bj * 3 + 2);
     float dot = 0.f;
@@ -244,41 +287,34 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_bwd(const float* __restrict
       dot = gx * __ldg(coords_out + bj * 3) + gy * __ldg(coords_out + bj * 3 + 1) + gz * __ldg(coords_out + bj * 3 + 2);
       if (HAS_GP) dot += __ldg(dots + bj);
     }
-    const float* prow = prob + bj * nvox;
-    const float* grow = HAS_GP ? gprob + bj * nvox : nullptr;
     float* orow = gvol + bj * nvox;
 #pragma unroll
     for (int i = 0; i < kSamEpt / 4; ++i) {
       const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
-      float p[4], gp[4] = {0.f, 0.f, 0.f, 0.f}, o[4];
-      if (VEC) {
-        if (v0 >= nvox) continue;
-        float4 t = ldg128_stream(prow + v0);
-        p[0] = t.x; p[1] = t.y; p[2] = t.z; p[3] = t.w;
-        if (HAS_GP) {
-          float4 u = ldg128_stream(grow + v0);
-          gp[0] = u.x; gp[1] = u.y; gp[2] = u.z; gp[3] = u.w;
-        }
-      } else {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          p[e] = (v0 + e < nvox) ? __ldg(prow + v0 + e) : 0.f;
-          if (HAS_GP) gp[e] = (v0 + e < nvox) ? __ldg(grow + v0 + e) : 0.f;
-        }
-      }
+      float o[4];
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        const float G = gp[e] + (gx * cx[i * 4 + e] + gy * cy[i * 4 + e] + gz * cz[i * 4 + e]);
-        if (SOFTMAX) o[e] = mult * (p[e] * (G - dot));
-        else o[e] = (p[e] > 0.f) ? mult * G : 0.f;
+        const float G = gp[i * 4 + e] + (gx * cx[i * 4 + e] + gy * cy[i * 4 + e] + gz * cz[i * 4 + e]);
+        if (SOFTMAX) o[e] = mult * (p[i * 4 + e] * (G - dot));
+        else o[e] = (p[i * 4 + e] > 0.f) ? mult * G : 0.f;
       }
       if (VEC) {
-        stg128_stream(orow + v0, make_float4(o[0], o[1], o[2], o[3]));
+        if (v0 < nvox) stg128_stream(orow + v0, make_float4(o[0], o[1], o[2], o[3]));
       } else {
 #pragma unroll
         for (int e = 0; e < 4; ++e)
           if (v0 + e < nvox) orow[v0 + e] = o[e];
       }
+    }
+  };
+  float pa[kSamEpt], pb[kSamEpt], ga[kSamEpt], gb[kSamEpt];
+  if (J > 0) load_rows(0, pa, ga);
+  for (int j = 0; j < J; j += 2) {
+    if (j + 1 < J) load_rows(j + 1, pb, gb);
+    emit(j, pa, ga);
+    if (j + 1 < J) {
+      if (j + 2 < J) load_rows(j + 2, pa, ga);
+      emit(j + 1, pb, gb);
     }
   }
 }

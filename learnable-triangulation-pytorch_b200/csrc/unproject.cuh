@@ -183,10 +183,14 @@ __device__ __forceinline__ void gather4(const float* __restrict__ fv, int off, c
   const float4 t01 = ldg128_nc(p + Cp);
   const float4 t10 = ldg128_nc(p + rowStride);
   const float4 t11 = ldg128_nc(p + rowStride + Cp);
-  s[0] = fmaf(t11.x, w.w, fmaf(t10.x, w.z, fmaf(t01.x, w.y, t00.x * w.x)));
-  s[1] = fmaf(t11.y, w.w, fmaf(t10.y, w.z, fmaf(t01.y, w.y, t00.y * w.x)));
-  s[2] = fmaf(t11.z, w.w, fmaf(t10.z, w.z, fmaf(t01.z, w.y, t00.z * w.x)));
-  s[3] = fmaf(t11.w, w.w, fmaf(t10.w, w.z, fmaf(t01.w, w.y, t00.w * w.x)));
+  // two channels per FFMA2 (the weight operand is broadcast by the instruction): same nw, ne, sw, se chain per channel
+  const f2 wx = pack2(w.x, w.x), wy = pack2(w.y, w.y), wz = pack2(w.z, w.z), ww = pack2(w.w, w.w);
+  f2 lo = mul2(pack2(t00.x, t00.y), wx), hi = mul2(pack2(t00.z, t00.w), wx);
+  lo = fma2(pack2(t01.x, t01.y), wy, lo); hi = fma2(pack2(t01.z, t01.w), wy, hi);
+  lo = fma2(pack2(t10.x, t10.y), wz, lo); hi = fma2(pack2(t10.z, t10.w), wz, hi);
+  lo = fma2(pack2(t11.x, t11.y), ww, lo); hi = fma2(pack2(t11.z, t11.w), ww, hi);
+  unpack2(lo, s[0], s[1]);
+  unpack2(hi, s[2], s[3]);
 }
 
 void fill_unproj_tiling(UnprojArgs& a, int lpv);

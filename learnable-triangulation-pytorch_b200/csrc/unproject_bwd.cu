@@ -24,10 +24,28 @@ __device__ __forceinline__ void scatter4(float* __restrict__ gv, int off, const 
   float* p = gv + off;
   const int dx = Cp;
   const int dy = rowStride;
-  if (w.x != 0.f) red_add_v4(p, d[0] * w.x, d[1] * w.x, d[2] * w.x, d[3] * w.x);
-  if (w.y != 0.f) red_add_v4(p + dx, d[0] * w.y, d[1] * w.y, d[2] * w.y, d[3] * w.y);
-  if (w.z != 0.f) red_add_v4(p + dy, d[0] * w.z, d[1] * w.z, d[2] * w.z, d[3] * w.z);
-  if (w.w != 0.f) red_add_v4(p + dy + dx, d[0] * w.w, d[1] * w.w, d[2] * w.w, d[3] * w.w);
+  const f2 dlo = pack2(d[0], d[1]), dhi = pack2(d[2], d[3]);
+  float a0, a1, a2, a3;
+  if (w.x != 0.f) {
+    const f2 ws = pack2(w.x, w.x);
+    unpack2(mul2(dlo, ws), a0, a1); unpack2(mul2(dhi, ws), a2, a3);
+    red_add_v4(p, a0, a1, a2, a3);
+  }
+  if (w.y != 0.f) {
+    const f2 ws = pack2(w.y, w.y);
+    unpack2(mul2(dlo, ws), a0, a1); unpack2(mul2(dhi, ws), a2, a3);
+    red_add_v4(p + dx, a0, a1, a2, a3);
+  }
+  if (w.z != 0.f) {
+    const f2 ws = pack2(w.z, w.z);
+    unpack2(mul2(dlo, ws), a0, a1); unpack2(mul2(dhi, ws), a2, a3);
+    red_add_v4(p + dy, a0, a1, a2, a3);
+  }
+  if (w.w != 0.f) {
+    const f2 ws = pack2(w.w, w.w);
+    unpack2(mul2(dlo, ws), a0, a1); unpack2(mul2(dhi, ws), a2, a3);
+    red_add_v4(p + dy + dx, a0, a1, a2, a3);
+  }
 }
 
 // common prologue of the backward kernels
