@@ -116,8 +116,9 @@ def launches_per_step(w, B, nvox):
 class DeviceStep:
     """Preallocated buffers + one method that enqueues the whole step (optionally with an event after each stage)."""
 
-    def __init__(self, w, B, dev, seed):
+    def __init__(self, w, B, dev, seed, slab_world=1):
         import lt_b200
+        self.slab_world = slab_world
         from lt_b200 import _lib, synthetic
         self.L, self.lib, self.w, self.B, self.dev = _lib.lib(), _lib, w, B, dev
         conf = "conf" if w["agg"] == "conf" else None
@@ -141,6 +142,7 @@ class DeviceStep:
         self.coords = torch.empty((B, w["J"], 3), device=dev)
         self.prob = torch.empty_like(self.x)
         self.stats = torch.empty((B, w["J"], 5), device=dev)
+        self.parts = torch.empty((slab_world, B, w["J"], 5), device=dev)
         self.gcoords = torch.randn((B, w["J"], 3), generator=g).to(dev)
         self.gx = torch.empty_like(self.x)
         self.gfeat_hwc = torch.empty_like(self.feat_hwc)
@@ -166,8 +168,18 @@ class DeviceStep:
         chk(L.lt_unproject_fwd(p(self.feat_hwc), p(self.proj), p(self.coord), p(self.conf), p(self.vol), B, w["V"],
                                w["C"], w["H"], w["W"], N0, N1, N2, self.agg, 0, st))
         mark(2)
-        chk(L.lt_softargmax_fwd(p(self.x), p(self.coord), p(self.coords), p(self.prob), p(self.stats), p(self.ws), B,
-                                w["J"], self.nvox, 1, 1.0, st))
+        if self.slab_world > 1:
+            # z-slab sharded soft-argmax (cfg5): slab-local tuples, ONE small all_gather over NCCL, fixed-order merge
+            import torch.distributed as dist
+            chk(L.lt_softargmax_partial(p(self.x), p(self.coord), p(self.stats), p(self.ws), B, w["J"], self.nvox, 1,
+                                        1.0, st))
+            dist.all_gather_into_tensor(self.parts.view(-1), self.stats.view(-1))
+            chk(L.lt_softargmax_merge(p(self.parts), p(self.stats), self.slab_world, B * w["J"], 1, st))
+            chk(L.lt_softargmax_finalize(p(self.x), p(self.stats), p(self.coords), p(self.prob), B, w["J"], self.nvox,
+                                         1, 1.0, st))
+        else:
+            chk(L.lt_softargmax_fwd(p(self.x), p(self.coord), p(self.coords), p(self.prob), p(self.stats), p(self.ws),
+                                    B, w["J"], self.nvox, 1, 1.0, st))
         mark(3)
         chk(L.lt_softargmax_bwd(p(self.prob), p(self.coord), p(self.coords), p(self.gcoords), None, None, p(self.gx),
                                 B, w["J"], self.nvox, 1, 1.0, st))
@@ -338,8 +350,9 @@ def main():
         from lt_b200.slab import slab_bounds
         lo, hi = slab_bounds(w["N"], world, rank)
         w["N0"] = hi - lo
-    total_B = B * world
-    step = DeviceStep(w, B, dev, seed=rank)
+    total_B = w["B"] if args.workload == "cfg5" else B * world   # cfg5: ONE volume shared by all ranks (z-slabs)
+    slab_world = world if args.workload == "cfg5" else 1
+    step = DeviceStep(w, B, dev, seed=(0 if slab_world > 1 else rank), slab_world=slab_world)
     flush = None if "larger" in config["cache"] else torch.empty(64 * 1024 * 1024, device=dev)
 
     def barrier():

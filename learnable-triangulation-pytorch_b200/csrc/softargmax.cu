@@ -137,33 +137,47 @@ __global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __res
   }
 }
 
-// merge P tuples per (b,j): one warp each, lanes stride over the tuples, then a fixed butterfly.
+// merge P tuples per (b,j): one CTA each (a 256^3 volume has 65536 partial tuples per joint), threads stride over the
+// tuples, then a fixed warp butterfly and a fixed-order merge of the warp results: deterministic.
+constexpr int kCombThreads = 256;
 template <bool SOFTMAX>
-__global__ void k_sam_combine(const float* __restrict__ parts, float* __restrict__ stats, int P, int BJ,
-                              size_t part_stride /* floats between consecutive (b,j) */,
-                              size_t tuple_stride /* floats between consecutive tuples of one (b,j) */) {
-  const int bj = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(kCombThreads) k_sam_combine(const float* __restrict__ parts, float* __restrict__ stats,
+                                                              int P, int BJ, size_t part_stride /* floats between
+                                                              consecutive (b,j) */, size_t tuple_stride /* floats
+                                                              between consecutive tuples of one (b,j) */) {
+  __shared__ float s_part[kCombThreads / 32][5];
+  const int bj = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (bj >= BJ) return;
   const float* p = parts + (size_t)bj * part_stride;
   Lse5 acc = SOFTMAX ? lse_identity() : Lse5{0.f, 1.f, 0.f, 0.f, 0.f};
   if (SOFTMAX) {
-    for (int i = lane; i < P; i += 32) {
+    for (int i = threadIdx.x; i < P; i += kCombThreads) {
       const float* t = p + (size_t)i * tuple_stride;
       acc = lse_merge(acc, Lse5{t[0], t[1], t[2], t[3], t[4]});
     }
     acc = lse_warp_reduce(acc);
   } else {
     float x = 0.f, y = 0.f, z = 0.f;
-    for (int i = lane; i < P; i += 32) {
+    for (int i = threadIdx.x; i < P; i += kCombThreads) {
       const float* t = p + (size_t)i * tuple_stride;
       x += t[2]; y += t[3]; z += t[4];
     }
     acc = {0.f, 1.f, warp_sum(x), warp_sum(y), warp_sum(z)};
   }
   if (lane == 0) {
+    s_part[warp][0] = acc.m; s_part[warp][1] = acc.s; s_part[warp][2] = acc.x; s_part[warp][3] = acc.y; s_part[warp][4] = acc.z;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    Lse5 r = {s_part[0][0], s_part[0][1], s_part[0][2], s_part[0][3], s_part[0][4]};
+    for (int w = 1; w < kCombThreads / 32; ++w) {
+      const Lse5 o = {s_part[w][0], s_part[w][1], s_part[w][2], s_part[w][3], s_part[w][4]};
+      if (SOFTMAX) r = lse_merge(r, o);
+      else { r.x += o.x; r.y += o.y; r.z += o.z; }
+    }
     float* o = stats + (size_t)bj * 5;
-    o[0] = acc.m; o[1] = acc.s; o[2] = acc.x; o[3] = acc.y; o[4] = acc.z;
+    o[0] = r.m; o[1] = r.s; o[2] = r.x; o[3] = r.y; o[4] = r.z;
   }
 }
 
@@ -380,19 +394,17 @@ cudaError_t launch_softargmax_partial(const float* vol, const float* coord, floa
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const int P = nchunk * kSamWarps, BJ = B * J;
-  const int wpb = 4;
-  if (softmax) k_sam_combine<true><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
-  else k_sam_combine<false><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
+  if (softmax) k_sam_combine<true><<<BJ, kCombThreads, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
+  else k_sam_combine<false><<<BJ, kCombThreads, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
   return cudaGetLastError();
 }
 
 cudaError_t launch_softargmax_merge(const float* parts, float* merged, int R, int BJ, int softmax,
                                     cudaStream_t st) {
   if (BJ == 0) return cudaSuccess;
-  const int wpb = 4;
   // parts (R, BJ, 5): tuples of one (b,j) are BJ*5 floats apart
-  if (softmax) k_sam_combine<true><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(parts, merged, R, BJ, 5, (size_t)BJ * 5);
-  else k_sam_combine<false><<<(BJ + wpb - 1) / wpb, wpb * 32, 0, st>>>(parts, merged, R, BJ, 5, (size_t)BJ * 5);
+  if (softmax) k_sam_combine<true><<<BJ, kCombThreads, 0, st>>>(parts, merged, R, BJ, 5, (size_t)BJ * 5);
+  else k_sam_combine<false><<<BJ, kCombThreads, 0, st>>>(parts, merged, R, BJ, 5, (size_t)BJ * 5);
   return cudaGetLastError();
 }
 

@@ -26,7 +26,7 @@ constexpr int kWarpsPerCta = 8;   // arranged 4 (axis 0) x 2 (axis 1)
 constexpr int kWarpRuns0 = 2, kWarpRuns1 = 4;  // runs owned by a warp: 2 (axis 0) x 4 (axis 1)
 constexpr int kTile0 = 4 * kWarpRuns0, kTile1 = 2 * kWarpRuns1;  // CTA tile 8 x 8 (x 8 along the run axis)
 constexpr int kViewChunk = 4;     // views resolved per phase-A round
-constexpr int kMaxViewsSmem = 64; // projection matrices staged per CTA
+constexpr int kMaxViewsSmem = 32; // projection matrices staged per CTA
 constexpr int kMaxLanesPerVoxel = 32;  // => channel blocks of 128
 
 
