@@ -41,7 +41,9 @@ def test_host_side_entry_points_without_gpu():
     assert L.lt_abi_version() == 1
     assert L.lt_padded_channels(32) == 32 and L.lt_padded_channels(17) == 32
     assert L.lt_padded_channels(33) == 64 and L.lt_padded_channels(256) == 256 and L.lt_padded_channels(300) == 384
-    assert L.lt_softargmax_ws_bytes(16, 17, 64 ** 3) == 16 * 17 * 64 * 8 * 5 * 4
+    assert L.lt_softargmax_ws_bytes(16, 17, 64 ** 3) == 16 * 17 * 128 * 8 * 5 * 4   # 2048-voxel chunks, 8 warps, 5 floats
+    # gather layout: (BV, H+2, W+2, Cp) floats
+    assert L.lt_feat_layout_elems(8, 32, 96, 96) == 8 * 98 * 98 * 32 and L.lt_feat_layout_elems(2, 17, 5, 7) == 2 * 7 * 9 * 32
     # bad arguments come back as LT_ERR_INVALID with a message, nothing is launched
     rc = L.lt_dlt_fwd(None, None, None, None, None, 1, 0, 1, None)
     assert rc == -1 and b"LT_DLT_MAX_VIEWS" in L.lt_last_error()
