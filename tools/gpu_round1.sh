@@ -1,12 +1,12 @@
+# round evidence: parity suite, smoke, default bench (both arms), ncu launch list + full-set capture of every kernel of ours
 set -x
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
 python bench.py > gpurun_out/bench_cfg3.json 2> gpurun_out/bench_cfg3.err; echo "bench rc=$?"; cat gpurun_out/bench_cfg3.json
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2>&1; cat gpurun_out/bench_ref.json
 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu1.log 2>&1
 echo "ncu1 rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:'k_unproject|k_sam_stats|k_sam_final|k_sam_bwd|k_feat' -s 7 -c 7 -o gpurun_out/prof_r1 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'k_unproject|k_sam_stats|k_sam_final|k_sam_bwd|k_feat' -s 7 -c 7 -o gpurun_out/prof_round python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu2.log 2>&1
 echo "ncu2 rc=$?"
-ls -la gpurun_out
