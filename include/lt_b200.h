@@ -6,6 +6,7 @@
  *
  *   lt_unproject_*   replaces  mvn/utils/op.py:99-163     unproject_heatmaps (+ multiview.py:80-101 projection)
  *   lt_softargmax_*  replaces  mvn/utils/op.py:84-96      integrate_tensor_3d_with_coordinates
+ *   lt_softargmax2d_* replaces mvn/utils/op.py:11-47      integrate_tensor_2d
  *   lt_dlt_*         replaces  mvn/utils/multiview.py:132-174  triangulate_batch_of_points /
  *                                                              triangulate_point_from_multiple_views_linear_torch
  *
@@ -108,6 +109,18 @@ int lt_softargmax_bwd(const float *prob, const float *coord, const float *coords
                       const float *grad_coords, const float *grad_prob, const float *dots,
                       float *grad_vol, int B, int J, long long nvox, int softmax, float multiplier,
                       void *stream);
+
+/* ---- K4: 2-D soft-argmax of joint heat maps  (op.py:11-47 integrate_tensor_2d) -------------------
+ * hm (BJ, H, W) scaled by `multiplier` on the fly (triangulation.py:164 does heatmaps*heatmap_multiplier
+ * before the call).  softmax=1: prob = softmax over H*W, coords (BJ,2) = (sum p*x, sum p*y) in heat-map
+ * pixels.  softmax=0: prob = relu(hm) un-normalised (op.py:26) while coords = (sum p*x, sum p*y)/sum p
+ * (op.py:39-41; 0/0 = nan as in the reference).  The step that feeds lt_dlt_fwd in the algebraic net. */
+int lt_softargmax2d_fwd(const float *hm, float *coords, float *prob, int BJ, int H, int W, int softmax,
+                        float multiplier, void *stream);
+/* grad_coords (BJ,2); grad_prob (BJ,H,W) or NULL; prob/coords = saved outputs; grad_hm includes `multiplier`. */
+int lt_softargmax2d_bwd(const float *prob, const float *coords, const float *grad_coords,
+                        const float *grad_prob, float *grad_hm, int BJ, int H, int W, int softmax,
+                        float multiplier, void *stream);
 
 /* ---- K3: batched confidence-weighted DLT  (multiview.py:132-174) -------------------------------
  * proj (B,V,3,4)  pts (B,V,J,2)  conf (B,V,J) or NULL (=> ones, multiview.py:147-148)

@@ -157,6 +157,27 @@ LT_API int lt_softargmax_bwd(const float* prob, const float* coord, const float*
                                                     nvox, softmax ? 1 : 0, multiplier, as_stream(stream)));
 }
 
+LT_API int lt_softargmax2d_fwd(const float* hm, float* coords, float* prob, int BJ, int H, int W, int softmax,
+                        float multiplier, void* stream) {
+  LT_REQUIRE(BJ >= 0 && H >= 0 && W >= 0, "negative extent");
+  LT_REQUIRE((long long)H * W <= 0x7fffffffLL, "map too large");
+  LT_REQUIRE(multiplier > 0.f, "multiplier must be > 0 (scale on the caller side otherwise)");
+  if (BJ == 0) return 0;
+  LT_REQUIRE(coords && (H * W == 0 || (hm && prob)), "null pointer");
+  return finish(__func__, lt::launch_softargmax2d_fwd(hm, coords, prob, BJ, H, W, softmax ? 1 : 0, multiplier,
+                                                      as_stream(stream)));
+}
+
+LT_API int lt_softargmax2d_bwd(const float* prob, const float* coords, const float* grad_coords, const float* grad_prob,
+                        float* grad_hm, int BJ, int H, int W, int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(BJ >= 0 && H >= 0 && W >= 0, "negative extent");
+  LT_REQUIRE((long long)H * W <= 0x7fffffffLL, "map too large");
+  if ((long long)BJ * H * W == 0) return 0;
+  LT_REQUIRE(prob && coords && grad_coords && grad_hm, "null pointer");
+  return finish(__func__, lt::launch_softargmax2d_bwd(prob, coords, grad_coords, grad_prob, grad_hm, BJ, H, W,
+                                                      softmax ? 1 : 0, multiplier, as_stream(stream)));
+}
+
 LT_API int lt_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out, double* saved, int B, int V,
                int J, void* stream) {
   LT_REQUIRE(B >= 0 && J >= 0, "negative extent");

@@ -37,6 +37,12 @@ cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const f
                                   float* grad_vol, int B, int J, long long nvox, int softmax, float mult,
                                   cudaStream_t st);
 
+cudaError_t launch_softargmax2d_fwd(const float* hm, float* coords, float* prob, int BJ, int H, int W, int softmax,
+                                    float mult, cudaStream_t st);
+cudaError_t launch_softargmax2d_bwd(const float* prob, const float* coords, const float* grad_coords,
+                                    const float* grad_prob, float* grad_hm, int BJ, int H, int W, int softmax,
+                                    float mult, cudaStream_t st);
+
 cudaError_t launch_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out,
                            double* saved, int B, int V, int J, cudaStream_t st);
 cudaError_t launch_dlt_bwd(const float* grad_out, const float* proj, const float* pts, const float* conf,

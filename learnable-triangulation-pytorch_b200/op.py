@@ -6,6 +6,8 @@ Everything runs in hand-written sm_100a kernels behind the C ABI of ``include/lt
         reference: mvn/utils/op.py:99-163
     integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True)
         reference: mvn/utils/op.py:84-96
+    integrate_tensor_2d(heatmaps, softmax=True)
+        reference: mvn/utils/op.py:11-47
 """
 import torch
 
@@ -202,3 +204,57 @@ def integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True, *
         volumes = volumes * multiplier
         multiplier = 1.0
     return _SoftArgmax.apply(volumes, coord_volumes, 1 if softmax else 0, multiplier)
+
+
+class _SoftArgmax2D(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, heatmaps, softmax, multiplier):
+        L = _lib.lib()
+        B, J, H, W = heatmaps.shape
+        with torch.cuda.device(heatmaps.device):
+            hm = _f32c(heatmaps)
+            coords = torch.zeros((B, J, 2), device=hm.device, dtype=torch.float32)
+            prob = torch.empty(hm.shape, device=hm.device, dtype=torch.float32)
+            _lib.check(L.lt_softargmax2d_fwd(_lib.ptr(hm), _lib.ptr(coords), _lib.ptr(prob), B * J, H, W, softmax,
+                                             multiplier, _stream()))
+        ctx.save_for_backward(prob, coords)
+        ctx.meta = (B, J, H, W, softmax, multiplier, heatmaps.dtype)
+        ctx.set_materialize_grads(False)
+        return coords.to(heatmaps.dtype), prob.to(heatmaps.dtype)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_coords, g_prob):
+        L = _lib.lib()
+        prob, coords = ctx.saved_tensors
+        B, J, H, W, softmax, multiplier, dtype = ctx.meta
+        if not ctx.needs_input_grad[0]:
+            return None, None, None
+        with torch.cuda.device(prob.device):
+            ghm = torch.empty_like(prob)
+            if B * J * H * W > 0:
+                gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 2), device=prob.device)
+                gp = _f32c(g_prob) if g_prob is not None else None
+                _lib.check(L.lt_softargmax2d_bwd(_lib.ptr(prob), _lib.ptr(coords), _lib.ptr(gc), _lib.ptr(gp),
+                                                 _lib.ptr(ghm), B * J, H, W, softmax, multiplier, _stream()))
+        return ghm.to(dtype), None, None
+
+
+def integrate_tensor_2d(heatmaps, softmax=True, *, multiplier=1.0):
+    """Soft-argmax of joint heat maps in heat-map pixels (reference: op.py:11-47).
+
+    heatmaps (B,J,H,W). Returns ``(coordinates (B,J,2) as (x, y), heatmaps (B,J,H,W))`` where the second value is the
+    softmax-normalised map (softmax=True) or relu(heatmaps) un-normalised (softmax=False; the coordinates are then
+    divided by the total mass, op.py:39-41). ``multiplier`` (keyword only, default 1.0) fuses the
+    ``heatmaps * heatmap_multiplier`` of the caller (triangulation.py:164). Gradient flows from both outputs.
+    """
+    _require_cuda("heatmaps", heatmaps)
+    if heatmaps.dim() != 4:
+        # `batch_size, n_heatmaps, h, w = heatmaps.shape` (op.py:21) raises ValueError on any other rank
+        raise ValueError("not enough values to unpack (expected 4, got {})".format(heatmaps.dim())
+                         if heatmaps.dim() < 4 else "too many values to unpack (expected 4)")
+    multiplier = float(multiplier)
+    if not multiplier > 0.0:
+        heatmaps = heatmaps * multiplier
+        multiplier = 1.0
+    return _SoftArgmax2D.apply(heatmaps, 1 if softmax else 0, multiplier)

@@ -79,6 +79,26 @@ def run_softargmax(tag, softmax, **kw):
     npz("softargmax_%s" % tag, softmax=np.array(int(softmax)), **res)
 
 
+def run_softargmax2d(tag, softmax, B, J, H, W, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    hm0 = torch.randn(B, J, H, W, generator=g) * scale
+    res = {}
+    for dt, suffix in ((torch.float32, ""), (torch.float64, "64")):
+        hm = hm0.to(dt).clone().requires_grad_(True)
+        coords, prob = ref_op.integrate_tensor_2d(hm, softmax)
+        g2 = torch.Generator().manual_seed(seed + 80)
+        gc = torch.randn(coords.shape, generator=g2)
+        gp = torch.randn(prob.shape, generator=g2)
+        (g_c,) = torch.autograd.grad(coords, hm, gc.to(dt), retain_graph=True)
+        (g_b,) = torch.autograd.grad([coords, prob], hm, [gc.to(dt), gp.to(dt)])
+        if suffix == "":
+            res.update(heatmaps=hm0, coords=coords, prob=prob, grad_coords=gc, grad_prob=gp,
+                       grad_heatmaps_coords_only=g_c, grad_heatmaps_both=g_b)
+        else:
+            res.update(coords64=coords, prob64=prob, grad_heatmaps_coords_only64=g_c, grad_heatmaps_both64=g_b)
+    npz("softargmax2d_%s" % tag, softmax=np.array(int(softmax)), **res)
+
+
 def run_dlt(tag, **kw):
     d = syn.make_dlt_inputs(**kw)
     P, pts, conf = d["proj_matricies"], d["points"], d["confidences"]
@@ -124,6 +144,9 @@ def main():
     run_softargmax("small_softmax", True, B=2, J=3, N=(5, 6, 7), seed=21, train=True)
     run_softargmax("small_relu", False, B=2, J=3, N=(5, 6, 7), seed=22, train=True)
     run_softargmax("peaked_softmax", True, B=1, J=3, N=12, seed=23, peaked=True, train=True)
+    run_softargmax2d("small_softmax", True, B=2, J=3, H=7, W=9, seed=41)
+    run_softargmax2d("small_relu", False, B=2, J=3, H=7, W=9, seed=42)
+    run_softargmax2d("sharp_softmax", True, B=1, J=4, H=24, W=24, seed=43, scale=100.0)   # heatmap_multiplier = 100
     run_dlt("conf", B=3, V=4, J=5, seed=31)
     run_dlt("noconf", B=2, V=3, J=4, seed=32, with_conf=False)
     run_dlt("manyview", B=1, V=31, J=6, seed=33, dome=True)

@@ -233,6 +233,26 @@ class CpuSlabOps:
 
 
 # --------------------------------------------------------------------------------------------------------------------
+# 2-D soft-argmax of joint heat maps  (reference: mvn/utils/op.py:11-47)
+# --------------------------------------------------------------------------------------------------------------------
+def integrate_tensor_2d(heatmaps, softmax=True):
+    """heatmaps (B,J,H,W) -> ((B,J,2) as (x, y), (B,J,H,W)). Same operation sequence as the reference: softmax or relu
+    over the flattened map (op.py:23-27), marginal masses (op.py:31-32) times arange (op.py:34-35); relu mode divides
+    the coordinates by the total mass (op.py:39-41) and returns the un-normalised relu maps."""
+    B, J, H, W = heatmaps.shape
+    flat = heatmaps.reshape(B, J, -1)
+    flat = F.softmax(flat, dim=2) if softmax else F.relu(flat)
+    hm = flat.reshape(B, J, H, W)
+    mass_x, mass_y = hm.sum(dim=2), hm.sum(dim=3)
+    x = (mass_x * torch.arange(W, dtype=hm.dtype)).sum(dim=2, keepdim=True)
+    y = (mass_y * torch.arange(H, dtype=hm.dtype)).sum(dim=2, keepdim=True)
+    if not softmax:
+        x = x / mass_x.sum(dim=2, keepdim=True)
+        y = y / mass_y.sum(dim=2, keepdim=True)
+    return torch.cat((x, y), dim=2), hm
+
+
+# --------------------------------------------------------------------------------------------------------------------
 # batched DLT  (reference: mvn/utils/multiview.py:132-174)
 # --------------------------------------------------------------------------------------------------------------------
 def dlt_system(proj, pts, conf=None):

@@ -20,6 +20,9 @@ def test_signatures_match_reference():
     assert all(sig.parameters[n].kind is inspect.Parameter.KEYWORD_ONLY for n in names[5:])
     sig = inspect.signature(lt_b200.op.integrate_tensor_3d_with_coordinates)
     assert list(sig.parameters)[:3] == ["volumes", "coord_volumes", "softmax"] and sig.parameters["softmax"].default is True
+    sig = inspect.signature(lt_b200.op.integrate_tensor_2d)
+    assert list(sig.parameters)[:2] == ["heatmaps", "softmax"] and sig.parameters["softmax"].default is True
+    assert sig.parameters["multiplier"].kind is inspect.Parameter.KEYWORD_ONLY
     sig = inspect.signature(lt_b200.multiview.triangulate_batch_of_points)
     assert list(sig.parameters) == ["proj_matricies_batch", "points_batch", "confidences_batch"]
     sig = inspect.signature(lt_b200.multiview.triangulate_point_from_multiple_views_linear_torch)
@@ -37,6 +40,8 @@ def test_error_conventions():
         lt_b200.unproject_heatmaps(d["heatmaps"], d["proj_matricies"], d["coord_volumes"], "sum")
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         lt_b200.integrate_tensor_3d_with_coordinates(torch.zeros(1, 2, 4, 4, 4), d["coord_volumes"])
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        lt_b200.integrate_tensor_2d(torch.zeros(1, 2, 4, 4))
     dl = synthetic.make_dlt_inputs(B=1, V=3, J=2)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         lt_b200.triangulate_batch_of_points(dl["proj_matricies"], dl["points"], dl["confidences"])
@@ -84,6 +89,7 @@ def test_patch_reference_swaps_the_three_call_sites():
         assert ref_op.unproject_heatmaps is lt_b200.op.unproject_heatmaps
         assert ref_op.integrate_tensor_3d_with_coordinates is lt_b200.op.integrate_tensor_3d_with_coordinates
         assert ref_mv.triangulate_batch_of_points is lt_b200.multiview.triangulate_batch_of_points
+        assert ref_op.integrate_tensor_2d is lt_b200.op.integrate_tensor_2d
         lt_b200.unpatch_reference()
         assert ref_op.unproject_heatmaps is orig
     finally:

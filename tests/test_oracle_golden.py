@@ -74,6 +74,18 @@ def test_softargmax_slab_pieces(name):
         assert rel_err(torch.cat(probs, dim=2), g["prob64"]) < 1e-5
 
 
+@pytest.mark.parametrize("name", golden_names("softargmax2d_"))
+def test_softargmax2d_matches_reference(name):
+    g = load_golden(name)
+    hm = g["heatmaps"].clone().requires_grad_(True)
+    coords, prob = ref_ops.integrate_tensor_2d(hm, bool(g["softmax"]))
+    assert torch.allclose(coords, g["coords"], rtol=1e-6, atol=1e-6) and torch.allclose(prob, g["prob"], rtol=1e-6, atol=1e-9)
+    (gh,) = torch.autograd.grad([coords, prob], hm, [g["grad_coords"], g["grad_prob"]])
+    assert rel_err(gh, g["grad_heatmaps_both"]) < 1e-6
+    c64, p64 = ref_ops.integrate_tensor_2d(g["heatmaps"].double(), bool(g["softmax"]))
+    assert torch.allclose(c64, g["coords64"], rtol=1e-12, atol=1e-12) and torch.allclose(p64, g["prob64"], rtol=1e-12, atol=1e-15)
+
+
 @pytest.mark.parametrize("name", golden_names("dlt_"))
 def test_dlt_matches_reference(name):
     g = load_golden(name)
