@@ -7,6 +7,7 @@
  *   lt_unproject_*   replaces  mvn/utils/op.py:99-163     unproject_heatmaps (+ multiview.py:80-101 projection)
  *   lt_softargmax_*  replaces  mvn/utils/op.py:84-96      integrate_tensor_3d_with_coordinates
  *   lt_softargmax2d_* replaces mvn/utils/op.py:11-47      integrate_tensor_2d
+ *   lt_volce_*        replaces mvn/models/loss.py:52-80   VolumetricCELoss.forward
  *   lt_dlt_*         replaces  mvn/utils/multiview.py:132-174  triangulate_batch_of_points /
  *                                                              triangulate_point_from_multiple_views_linear_torch
  *
@@ -121,6 +122,19 @@ int lt_softargmax2d_fwd(const float *hm, float *coords, float *prob, int BJ, int
 int lt_softargmax2d_bwd(const float *prob, const float *coords, const float *grad_coords,
                         const float *grad_prob, float *grad_hm, int BJ, int H, int W, int softmax,
                         float multiplier, void *stream);
+
+/* ---- K5: volumetric cross-entropy loss  (mvn/models/loss.py:52-80 VolumetricCELoss) --------------
+ * coord (B,nvox,3)  prob (B,J,nvox) = second output of lt_softargmax_fwd  kp_gt (B,J,3)  validity (B,J)
+ * loss (1) = sum_{b,j} validity * -log(prob[b,j,i*] + 1e-6) / (B*J),  i* = first argmin_i |coord_i - kp_gt_bj|
+ * (fp32 distances in the reference's operation order, loss.py:66-70).  idx (B,J) int32 receives i* for the
+ * backward.  ws: lt_volce_ws_bytes bytes of scratch.  No host synchronisation (loss.py:71 copies the indices to
+ * the host).  B*J > 0 is required: the reference divides by n_losses = B*J (loss.py:80). */
+size_t lt_volce_ws_bytes(int B, int J, long long nvox);
+int lt_volce_fwd(const float *coord, const float *prob, const float *kp_gt, const float *validity,
+                 float *loss, int *idx, void *ws, int B, int J, long long nvox, void *stream);
+/* grad_loss (1) on the device; grad_prob (B,J,nvox) is fully overwritten: zeros except the B*J voxels idx. */
+int lt_volce_bwd(const float *prob, const int *idx, const float *validity, const float *grad_loss,
+                 float *grad_prob, int B, int J, long long nvox, void *stream);
 
 /* ---- K3: batched confidence-weighted DLT  (multiview.py:132-174) -------------------------------
  * proj (B,V,3,4)  pts (B,V,J,2)  conf (B,V,J) or NULL (=> ones, multiview.py:147-148)

@@ -178,6 +178,26 @@ LT_API int lt_softargmax2d_bwd(const float* prob, const float* coords, const flo
                                                       softmax ? 1 : 0, multiplier, as_stream(stream)));
 }
 
+LT_API size_t lt_volce_ws_bytes(int B, int J, long long nvox) { return lt::volce_ws_bytes(B, J, nvox); }
+
+LT_API int lt_volce_fwd(const float* coord, const float* prob, const float* kp_gt, const float* validity, float* loss,
+                 int* idx, void* ws, int B, int J, long long nvox, void* stream) {
+  LT_REQUIRE(B >= 1 && J >= 1 && nvox >= 1, "need B, J, nvox >= 1 (the reference divides by B*J)");
+  LT_REQUIRE(B <= 65535, "B > 65535");
+  LT_REQUIRE(nvox <= 0x7fffffffLL, "nvox does not fit the int32 index");
+  LT_REQUIRE(coord && prob && kp_gt && validity && loss && idx && ws, "null pointer");
+  return finish(__func__, lt::launch_volce_fwd(coord, prob, kp_gt, validity, loss, idx, ws, B, J, nvox,
+                                               as_stream(stream)));
+}
+
+LT_API int lt_volce_bwd(const float* prob, const int* idx, const float* validity, const float* grad_loss,
+                 float* grad_prob, int B, int J, long long nvox, void* stream) {
+  LT_REQUIRE(B >= 1 && J >= 1 && nvox >= 1, "need B, J, nvox >= 1");
+  LT_REQUIRE(prob && idx && validity && grad_loss && grad_prob, "null pointer");
+  return finish(__func__, lt::launch_volce_bwd(prob, idx, validity, grad_loss, grad_prob, B, J, nvox,
+                                               as_stream(stream)));
+}
+
 LT_API int lt_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out, double* saved, int B, int V,
                int J, void* stream) {
   LT_REQUIRE(B >= 0 && J >= 0, "negative extent");

@@ -7,6 +7,7 @@ those attributes is the whole integration.
 """
 import importlib
 
+from . import loss as _loss
 from . import multiview as _mv
 from . import op as _op
 
@@ -17,6 +18,9 @@ _TARGETS = (
     ("mvn.utils.multiview", "triangulate_batch_of_points", _mv.triangulate_batch_of_points),
     ("mvn.utils.multiview", "triangulate_point_from_multiple_views_linear_torch",
      _mv.triangulate_point_from_multiple_views_linear_torch),
+    # train.py:26 binds the class with `from mvn.models.loss import ...`: patch BEFORE importing train.py
+    # (train.py:225 instantiates it per iteration, so the module attribute is what has to change)
+    ("mvn.models.loss", "VolumetricCELoss", _loss.VolumetricCELoss),
 )
 
 _saved = {}

@@ -99,6 +99,41 @@ def run_softargmax2d(tag, softmax, B, J, H, W, seed, scale=1.0):
     npz("softargmax2d_%s" % tag, softmax=np.array(int(softmax)), **res)
 
 
+def run_volce(tag, B, J, N, seed, spread):
+    """The unmodified VolumetricCELoss (mvn/models/loss.py:52-80) on the softmaxed volumes of the unmodified
+    integrate_tensor_3d_with_coordinates; ground-truth joints = predicted joints + N(0, spread mm)."""
+    from mvn.models.loss import VolumetricCELoss
+    d = syn.make_softargmax_inputs(B=B, J=J, N=N, seed=seed, train=True, peaked=True)
+    g = torch.Generator().manual_seed(seed + 81)
+    res = {}
+    for dt, suffix in ((torch.float32, ""), (torch.float64, "64")):
+        vol = d["volumes"].to(dt).clone().requires_grad_(True)
+        coords, prob = ref_op.integrate_tensor_3d_with_coordinates(vol, d["coord_volumes"].to(dt), softmax=True)
+        if suffix == "":
+            kp_gt = (coords.detach() + spread * torch.randn(coords.shape, generator=g)).float()
+            validity = (torch.rand(B, J, 1, generator=g) > 0.25).float()
+            validity[0, 0, 0] = 0.0
+        prob_leaf = prob.detach().clone().requires_grad_(True)
+        loss = VolumetricCELoss()(d["coord_volumes"].to(dt), prob_leaf, kp_gt.to(dt), validity.to(dt))
+        (gp,) = torch.autograd.grad(loss, prob_leaf)
+        if suffix == "":
+            res.update(coord_volumes=d["coord_volumes"], prob=prob.detach(), keypoints_gt=kp_gt, validity=validity,
+                       loss=loss.detach(), grad_prob=gp,
+                       nearest=ref_nearest(d["coord_volumes"], kp_gt))
+        else:
+            res.update(loss64=loss.detach(), grad_prob64=gp)
+    npz("volce_%s" % tag, **res)
+
+
+def ref_nearest(coord_volumes, kp_gt):
+    # the argmin statements of loss.py:63-71, kept as flat indices
+    out = []
+    for b in range(coord_volumes.shape[0]):
+        dists = torch.sqrt(((coord_volumes[b].unsqueeze(0) - kp_gt[b].unsqueeze(1).unsqueeze(1).unsqueeze(1)) ** 2).sum(-1))
+        out.append(torch.argmin(dists.view(dists.shape[0], -1), dim=-1))
+    return torch.stack(out)
+
+
 def run_dlt(tag, **kw):
     d = syn.make_dlt_inputs(**kw)
     P, pts, conf = d["proj_matricies"], d["points"], d["confidences"]
@@ -147,6 +182,8 @@ def main():
     run_softargmax2d("small_softmax", True, B=2, J=3, H=7, W=9, seed=41)
     run_softargmax2d("small_relu", False, B=2, J=3, H=7, W=9, seed=42)
     run_softargmax2d("sharp_softmax", True, B=1, J=4, H=24, W=24, seed=43, scale=100.0)   # heatmap_multiplier = 100
+    run_volce("small", B=2, J=3, N=(5, 6, 7), seed=51, spread=150.0)
+    run_volce("cube12", B=2, J=4, N=12, seed=52, spread=60.0)
     run_dlt("conf", B=3, V=4, J=5, seed=31)
     run_dlt("noconf", B=2, V=3, J=4, seed=32, with_conf=False)
     run_dlt("manyview", B=1, V=31, J=6, seed=33, dome=True)

@@ -253,6 +253,36 @@ def integrate_tensor_2d(heatmaps, softmax=True):
 
 
 # --------------------------------------------------------------------------------------------------------------------
+# volumetric cross-entropy loss  (reference: mvn/models/loss.py:52-80)
+# --------------------------------------------------------------------------------------------------------------------
+def volumetric_ce_loss(coord_volumes_batch, volumes_batch_pred, keypoints_gt, keypoints_binary_validity):
+    """Same statements as VolumetricCELoss.forward: per batch item the (J, N^3) distances of every voxel centre to
+    every ground-truth joint (loss.py:63-69), argmin -> host indices (loss.py:71-72), then validity * -log(p + 1e-6)
+    per joint in a python loop (loss.py:74-77), divided by the number of (b, j) pairs (loss.py:80)."""
+    loss, n_losses = 0.0, 0
+    for b in range(volumes_batch_pred.shape[0]):
+        cv = coord_volumes_batch[b].unsqueeze(0)
+        kp = keypoints_gt[b].unsqueeze(1).unsqueeze(1).unsqueeze(1)
+        dists = torch.sqrt(((cv - kp) ** 2).sum(-1))
+        dists = dists.view(dists.shape[0], -1)
+        flat = torch.argmin(dists, dim=-1).detach().cpu().numpy()
+        idx = np.stack(np.unravel_index(flat, volumes_batch_pred.shape[-3:]), axis=1)
+        for j, ix in enumerate(idx):
+            loss = loss + keypoints_binary_validity[b, j][0] * (-torch.log(volumes_batch_pred[b, j, ix[0], ix[1], ix[2]] + 1e-6))
+            n_losses += 1
+    return loss / n_losses
+
+
+def volumetric_ce_nearest_voxels(coord_volumes_batch, keypoints_gt):
+    """(B, J) flat index of the voxel nearest to each joint: the argmin of loss.py:66-71 on its own."""
+    out = []
+    for b in range(coord_volumes_batch.shape[0]):
+        d = torch.sqrt(((coord_volumes_batch[b].unsqueeze(0) - keypoints_gt[b].view(-1, 1, 1, 1, 3)) ** 2).sum(-1))
+        out.append(torch.argmin(d.view(d.shape[0], -1), dim=-1))
+    return torch.stack(out)
+
+
+# --------------------------------------------------------------------------------------------------------------------
 # batched DLT  (reference: mvn/utils/multiview.py:132-174)
 # --------------------------------------------------------------------------------------------------------------------
 def dlt_system(proj, pts, conf=None):

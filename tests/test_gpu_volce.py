@@ -1,0 +1,104 @@
+"""GPU: K5 (VolumetricCELoss, mvn/models/loss.py:52-80) through the C ABI against golden vectors of the unmodified
+reference class, the oracle at the BASELINE volume size, and known answers. The nearest-voxel indices must be
+bit-identical (integer work); the loss and its gradient agree to fp32 log/division rounding (1e-6 / 1e-5 relative)."""
+import pytest
+import torch
+
+import lt_b200
+from conftest import golden_names, load_golden, rel_err
+from lt_b200 import synthetic
+from oracle import ref_ops
+
+pytestmark = pytest.mark.gpu
+
+
+def _nearest_from_grad(gp):
+    """flat index of the single non-zero of each (b, j) gradient row, -1 for rows without one"""
+    flat = gp.flatten(2)
+    nz = flat != 0
+    return torch.where(nz.any(-1), nz.float().argmax(-1), torch.full(nz.shape[:2], -1, device=gp.device))
+
+
+@pytest.mark.parametrize("name", golden_names("volce_"))
+def test_golden_forward_backward(name):
+    g = load_golden(name)
+    prob = g["prob"].cuda().requires_grad_(True)
+    crit = lt_b200.VolumetricCELoss()
+    loss = crit(g["coord_volumes"].cuda(), prob, g["keypoints_gt"].cuda(), g["validity"].cuda())
+    assert loss.dim() == 0 and loss.dtype == torch.float32
+    assert abs(loss.item() - g["loss"]) <= 1e-6 * abs(g["loss"])
+    assert abs(loss.item() - g["loss64"]) <= 1e-5 * abs(g["loss64"])
+    (gp,) = torch.autograd.grad(loss, prob)
+    assert rel_err(gp.cpu(), g["grad_prob"]) < 1e-5
+    # integer part: exactly the reference's voxels
+    valid = g["validity"][:, :, 0] > 0
+    assert torch.equal(_nearest_from_grad(gp).cpu()[valid], g["nearest"][valid])
+    assert (gp.cpu()[~valid] == 0).all()
+
+
+@pytest.mark.parametrize("N", [64, (9, 17, 33)])
+def test_against_oracle_at_volume_size(N):
+    """BASELINE config-3 item shape (17 joints, 64^3) and a ragged volume (nvox % 4 != 0: scalar coordinate loads)."""
+    B, J = 3, 17
+    d = synthetic.make_softargmax_inputs(B=B, J=J, N=N, seed=5, train=True, peaked=True)
+    coord = d["coord_volumes"].cuda()
+    _, prob0 = lt_b200.integrate_tensor_3d_with_coordinates(d["volumes"].cuda(), coord, softmax=True)
+    gen = torch.Generator().manual_seed(9)
+    kp_gt = (torch.randn(B, J, 3, generator=gen) * 400.0 + coord.cpu().flatten(1, 3).mean(1, keepdim=True)).cuda()
+    kp_gt[0, 0] = coord[0, 0, 0, 0] - 1000.0           # far outside: nearest voxel is a corner
+    kp_gt[0, 1] = 0.5 * (coord[0, 2, 3, 4] + coord[0, 2, 3, 5])   # on the midpoint of two voxels
+    validity = (torch.rand(B, J, 1, generator=gen) > 0.2).float().cuda()
+    ref_idx = ref_ops.volumetric_ce_nearest_voxels(coord, kp_gt)
+    prob = prob0.detach().requires_grad_(True)
+    pref = prob0.detach().clone().requires_grad_(True)
+    loss = lt_b200.volumetric_ce_loss(coord, prob, kp_gt, validity)
+    ref = ref_ops.volumetric_ce_loss(coord, pref, kp_gt, validity)      # the reference's ops, CUDA tensors
+    assert abs(loss.item() - ref.item()) <= 2e-6 * abs(ref.item())
+    (gp,) = torch.autograd.grad(loss, prob, torch.tensor(2.5, device="cuda"))
+    (gr,) = torch.autograd.grad(ref, pref, torch.tensor(2.5, device="cuda"))
+    assert rel_err(gp, gr) < 1e-5
+    valid = validity[:, :, 0] > 0
+    assert torch.equal(_nearest_from_grad(gp)[valid], ref_idx[valid])
+
+
+def test_known_answers_and_errors():
+    # a one-hot volume at the voxel nearest to the joint -> -log(1 + 1e-6) ~ 0; a uniform volume -> log(nvox)
+    d = synthetic.make_softargmax_inputs(B=1, J=2, N=8, seed=1)
+    coord = d["coord_volumes"].cuda()
+    kp = torch.stack([coord[0, 3, 4, 5] + 1.0, coord[0, 7, 0, 2] - 1.0]).view(1, 2, 3)
+    vol = torch.zeros(1, 2, 8, 8, 8, device="cuda")
+    vol[0, 0, 3, 4, 5] = 1.0
+    vol[0, 1] = 1.0 / 512
+    ones = torch.ones(1, 2, 1, device="cuda")
+    loss = lt_b200.volumetric_ce_loss(coord, vol, kp, ones)
+    expect = 0.5 * (-torch.log(torch.tensor(1.0 + 1e-6)) - torch.log(torch.tensor(1.0 / 512 + 1e-6)))
+    assert abs(loss.item() - expect.item()) < 1e-6
+    # invalid joints do not contribute but still count in the denominator (loss.py:76-77)
+    half = lt_b200.volumetric_ce_loss(coord, vol, kp, torch.tensor([[[1.0], [0.0]]], device="cuda"))
+    assert abs(half.item() - 0.5 * -torch.log(torch.tensor(1.0 + 1e-6)).item()) < 1e-7
+    with pytest.raises(ZeroDivisionError):
+        lt_b200.volumetric_ce_loss(coord[:0], vol[:0], kp[:0], ones[:0])
+    with pytest.raises(RuntimeError):
+        lt_b200.volumetric_ce_loss(coord.cpu(), vol, kp, ones)
+    with pytest.raises(RuntimeError):
+        lt_b200.volumetric_ce_loss(coord[:, :4], vol, kp, ones)
+
+
+def test_chained_behind_the_soft_argmax():
+    """train.py:218-231: total = L(keypoints) + w * CE(volumes); both gradients meet in K2's backward."""
+    d = synthetic.make_softargmax_inputs(B=2, J=5, N=16, seed=3, train=True, peaked=True)
+    coord = d["coord_volumes"].cuda()
+    gen = torch.Generator().manual_seed(4)
+    outs = []
+    for integrate, ce in ((lt_b200.integrate_tensor_3d_with_coordinates, lt_b200.volumetric_ce_loss),
+                          (ref_ops.integrate_tensor_3d_with_coordinates, ref_ops.volumetric_ce_loss)):
+        vol = d["volumes"].cuda().requires_grad_(True)
+        kp, prob = integrate(vol, coord, softmax=True)
+        if not outs:
+            kp_gt = (kp.detach().cpu() + 80.0 * torch.randn(kp.shape, generator=gen)).cuda()
+            val = torch.ones(2, 5, 1, device="cuda")
+        total = ((kp - kp_gt) ** 2).sum().sqrt() + 0.01 * ce(coord, prob, kp_gt, val)
+        (gv,) = torch.autograd.grad(total, vol)
+        outs.append((total.item(), gv))
+    assert abs(outs[0][0] - outs[1][0]) < 1e-4 * abs(outs[1][0])
+    assert rel_err(outs[0][1], outs[1][1]) < 1e-4

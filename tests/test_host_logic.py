@@ -25,6 +25,9 @@ def test_signatures_match_reference():
     assert sig.parameters["multiplier"].kind is inspect.Parameter.KEYWORD_ONLY
     sig = inspect.signature(lt_b200.multiview.triangulate_batch_of_points)
     assert list(sig.parameters) == ["proj_matricies_batch", "points_batch", "confidences_batch"]
+    sig = inspect.signature(lt_b200.loss.VolumetricCELoss.forward)
+    assert list(sig.parameters) == ["self", "coord_volumes_batch", "volumes_batch_pred", "keypoints_gt",
+                                    "keypoints_binary_validity"]
     sig = inspect.signature(lt_b200.multiview.triangulate_point_from_multiple_views_linear_torch)
     assert list(sig.parameters) == ["proj_matricies", "points", "confidences"]
 
@@ -76,7 +79,6 @@ def test_slab_bounds_partition():
         assert max(sizes) - min(sizes) <= 1
 
 
-@pytest.mark.skipif(not os.path.isdir("/root/reference/mvn"), reason="reference tree not present")
 @pytest.mark.skipif(not os.path.isdir("/root/reference/mvn"), reason="the reference tree only exists in the build container")
 def test_patch_reference_swaps_the_three_call_sites():
     sys.path.insert(0, "/root/reference")
@@ -90,7 +92,13 @@ def test_patch_reference_swaps_the_three_call_sites():
         assert ref_op.integrate_tensor_3d_with_coordinates is lt_b200.op.integrate_tensor_3d_with_coordinates
         assert ref_mv.triangulate_batch_of_points is lt_b200.multiview.triangulate_batch_of_points
         assert ref_op.integrate_tensor_2d is lt_b200.op.integrate_tensor_2d
+        import mvn.models.loss as ref_loss
+        ref_ce = inspect.signature(lt_b200.VolumetricCELoss.forward)
+        assert ref_loss.VolumetricCELoss is lt_b200.loss.VolumetricCELoss
         lt_b200.unpatch_reference()
         assert ref_op.unproject_heatmaps is orig
+        # the drop-in class keeps the reference's forward signature (loss.py:56)
+        assert list(ref_ce.parameters) == list(inspect.signature(ref_loss.VolumetricCELoss.forward).parameters)
+        assert ref_loss.VolumetricCELoss is not lt_b200.loss.VolumetricCELoss
     finally:
         sys.path.remove("/root/reference")

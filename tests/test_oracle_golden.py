@@ -86,6 +86,22 @@ def test_softargmax2d_matches_reference(name):
     assert torch.allclose(c64, g["coords64"], rtol=1e-12, atol=1e-12) and torch.allclose(p64, g["prob64"], rtol=1e-12, atol=1e-15)
 
 
+@pytest.mark.parametrize("name", golden_names("volce_"))
+def test_volumetric_ce_matches_reference(name):
+    g = load_golden(name)
+    prob = g["prob"].clone().requires_grad_(True)
+    loss = ref_ops.volumetric_ce_loss(g["coord_volumes"], prob, g["keypoints_gt"], g["validity"])
+    assert loss.item() == g["loss"]                                   # same statements, same bits
+    (gp,) = torch.autograd.grad(loss, prob)
+    assert torch.equal(gp, g["grad_prob"])
+    assert torch.equal(ref_ops.volumetric_ce_nearest_voxels(g["coord_volumes"], g["keypoints_gt"]), g["nearest"])
+    assert int((g["grad_prob"] != 0).sum()) == int(g["validity"].sum())  # one non-zero per valid joint
+    l64 = ref_ops.volumetric_ce_loss(g["coord_volumes"].double(), g["prob"].double(), g["keypoints_gt"].double(),
+                                     g["validity"].double())
+    # the golden fp64 loss was taken on fp64 softmax volumes; these are the fp32 ones widened (1e-7 relative apart)
+    assert abs(l64.item() - g["loss64"]) < 1e-6
+
+
 @pytest.mark.parametrize("name", golden_names("dlt_"))
 def test_dlt_matches_reference(name):
     g = load_golden(name)
