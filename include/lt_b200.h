@@ -102,8 +102,9 @@ int lt_softargmax_merge(const float *parts, float *merged, int R, int BJ, int so
  * through the second return value, loss.py:76); prob = saved second output; coords = saved first
  * output (global coordinates, also in the slab-sharded case); grad_vol (B,J,nvox) includes the
  * `multiplier` factor.  softmax=1: g_i = p_i*(G_i - sum_k p_k G_k), G_i = gp_i + gc·xyz_i.
- * dots (B,J) is only used when grad_prob != NULL: lt_softargmax_bwd_dot fills it with
- * sum_k p_k*gp_k over THIS buffer (slab-sharded callers all-reduce it between the two calls). */
+ * dots (B,J) or NULL = sum_k p_k*gp_k: lt_softargmax_bwd_dot fills it from a dense grad_prob over THIS buffer
+ * (slab-sharded callers all-reduce it between the two calls); with grad_prob == NULL it carries a sparse
+ * upstream gradient (see lt_volce_bwd_sparse). Required when softmax && grad_prob. */
 int lt_softargmax_bwd_dot(const float *prob, const float *grad_prob, float *dots, void *ws, int B,
                           int J, long long nvox, void *stream);
 int lt_softargmax_bwd(const float *prob, const float *coord, const float *coords,
@@ -135,6 +136,17 @@ int lt_volce_fwd(const float *coord, const float *prob, const float *kp_gt, cons
 /* grad_loss (1) on the device; grad_prob (B,J,nvox) is fully overwritten: zeros except the B*J voxels idx. */
 int lt_volce_bwd(const float *prob, const int *idx, const float *validity, const float *grad_loss,
                  float *grad_prob, int B, int J, long long nvox, void *stream);
+
+/* The same gradient kept sparse, for callers that own both ops (no (B,J,nvox) gradient tensor between K5 and K2):
+ *   1. lt_volce_bwd_sparse        -> vals (B,J) = the non-zeros, dots (B,J) = prob[idx]*vals
+ *   2. lt_softargmax_bwd(..., grad_prob = NULL, dots, ...)   (dots without grad_prob = sparse upstream gradient)
+ *   3. lt_softargmax_bwd_add_sparse adds the B*J voxels' own G_i term into grad_vol. */
+int lt_volce_bwd_sparse(const float *prob, const int *idx, const float *validity,
+                        const float *grad_loss, float *vals, float *dots, int B, int J, long long nvox,
+                        void *stream);
+int lt_softargmax_bwd_add_sparse(const float *prob, const int *idx, const float *vals, float *grad_vol,
+                                 int B, int J, long long nvox, int softmax, float multiplier,
+                                 void *stream);
 
 /* ---- K3: batched confidence-weighted DLT  (multiview.py:132-174) -------------------------------
  * proj (B,V,3,4)  pts (B,V,J,2)  conf (B,V,J) or NULL (=> ones, multiview.py:147-148)

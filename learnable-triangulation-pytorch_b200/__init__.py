@@ -12,7 +12,7 @@ the repository root registers it under that name).
     lt_b200.patch_reference()                          monkey-patches the names above into ``mvn``
 """
 from . import _lib, loss, multiview, op, slab, synthetic  # noqa: F401
-from .loss import VolumetricCELoss, volumetric_ce_loss  # noqa: F401
+from .loss import VolumetricCELoss, integrate_tensor_3d_with_coordinates_and_ce, volumetric_ce_loss  # noqa: F401
 from .multiview import triangulate_batch_of_points, triangulate_point_from_multiple_views_linear_torch  # noqa: F401
 from .op import integrate_tensor_2d, integrate_tensor_3d_with_coordinates, unproject_heatmaps  # noqa: F401
 from .patch import patch_reference, unpatch_reference  # noqa: F401
@@ -20,6 +20,7 @@ from .patch import patch_reference, unpatch_reference  # noqa: F401
 __all__ = [
     "op", "multiview", "slab", "synthetic", "unproject_heatmaps", "integrate_tensor_3d_with_coordinates",
     "integrate_tensor_2d", "loss", "VolumetricCELoss", "volumetric_ce_loss",
+    "integrate_tensor_3d_with_coordinates_and_ce",
     "triangulate_batch_of_points", "triangulate_point_from_multiple_views_linear_torch", "patch_reference",
     "unpatch_reference",
 ]

@@ -198,6 +198,22 @@ LT_API int lt_volce_bwd(const float* prob, const int* idx, const float* validity
                                                as_stream(stream)));
 }
 
+LT_API int lt_volce_bwd_sparse(const float* prob, const int* idx, const float* validity, const float* grad_loss,
+                        float* vals, float* dots, int B, int J, long long nvox, void* stream) {
+  LT_REQUIRE(B >= 1 && J >= 1 && nvox >= 1, "need B, J, nvox >= 1");
+  LT_REQUIRE(prob && idx && validity && grad_loss && vals && dots, "null pointer");
+  return finish(__func__, lt::launch_volce_bwd_sparse(prob, idx, validity, grad_loss, vals, dots, B, J, nvox,
+                                                      as_stream(stream)));
+}
+
+LT_API int lt_softargmax_bwd_add_sparse(const float* prob, const int* idx, const float* vals, float* grad_vol, int B,
+                                 int J, long long nvox, int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(B >= 1 && J >= 1 && nvox >= 1, "need B, J, nvox >= 1");
+  LT_REQUIRE(prob && idx && vals && grad_vol, "null pointer");
+  return finish(__func__, lt::launch_softargmax_bwd_add_sparse(prob, idx, vals, grad_vol, B, J, nvox, softmax ? 1 : 0,
+                                                               multiplier, as_stream(stream)));
+}
+
 LT_API int lt_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out, double* saved, int B, int V,
                int J, void* stream) {
   LT_REQUIRE(B >= 0 && J >= 0, "negative extent");

@@ -40,6 +40,10 @@ cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const f
 size_t volce_ws_bytes(int B, int J, long long nvox);
 cudaError_t launch_volce_fwd(const float* coord, const float* prob, const float* kp, const float* validity, float* loss,
                              int* idx_out, void* ws, int B, int J, long long nvox, cudaStream_t st);
+cudaError_t launch_volce_bwd_sparse(const float* prob, const int* idx, const float* validity, const float* gloss,
+                                    float* vals, float* dots, int B, int J, long long nvox, cudaStream_t st);
+cudaError_t launch_softargmax_bwd_add_sparse(const float* prob, const int* idx, const float* vals, float* gvol, int B,
+                                             int J, long long nvox, int softmax, float mult, cudaStream_t st);
 cudaError_t launch_volce_bwd(const float* prob, const int* idx, const float* validity, const float* gloss, float* gvol,
                              int B, int J, long long nvox, cudaStream_t st);
 cudaError_t launch_softargmax2d_fwd(const float* hm, float* coords, float* prob, int BJ, int H, int W, int softmax,

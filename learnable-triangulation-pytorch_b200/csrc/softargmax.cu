@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_bwd(const float* __restrict
     float dot = 0.f;
     if (SOFTMAX) {
       dot = gx * __ldg(coords_out + bj * 3) + gy * __ldg(coords_out + bj * 3 + 1) + gz * __ldg(coords_out + bj * 3 + 2);
-      if (HAS_GP) dot += __ldg(dots + bj);
+      if (dots != nullptr) dot += __ldg(dots + bj);  // dense gp (k_sam_dot) or a sparse one (lt_volce_bwd_sparse)
     }
     float* orow = gvol + bj * nvox;
 #pragma unroll

@@ -136,6 +136,42 @@ __global__ void k_ce_bwd(const float* __restrict__ prob, const int* __restrict__
   gvol[at] = __fdiv_rn(__ldg(gloss), (float)BJ) * __ldg(validity + bj) * -__fdiv_rn(1.f, p + 1e-6f);
 }
 
+// The same gradient kept SPARSE for K2's backward (no (B,J,nvox) tensor): vals = the B*J non-zeros, dots = p*vals =
+// their contribution to the softmax-backward dot product; after lt_softargmax_bwd ran with these dots,
+// k_ce_add_sparse adds the G_i term of the B*J voxels themselves.
+__global__ void k_ce_bwd_sparse(const float* __restrict__ prob, const int* __restrict__ idx,
+                                const float* __restrict__ validity, const float* __restrict__ gloss,
+                                float* __restrict__ vals, float* __restrict__ dots, int BJ, long long nvox) {
+  const int bj = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bj >= BJ) return;
+  const float p = __ldg(prob + (size_t)bj * nvox + idx[bj]);
+  const float v = __fdiv_rn(__ldg(gloss), (float)BJ) * __ldg(validity + bj) * -__fdiv_rn(1.f, p + 1e-6f);
+  vals[bj] = v;
+  dots[bj] = p * v;
+}
+__global__ void k_ce_add_sparse(const float* __restrict__ prob, const int* __restrict__ idx,
+                                const float* __restrict__ vals, float* __restrict__ gvol, int BJ, long long nvox,
+                                int softmax, float mult) {
+  const int bj = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bj >= BJ) return;
+  const size_t at = (size_t)bj * nvox + idx[bj];
+  const float p = __ldg(prob + at);
+  gvol[at] += softmax ? mult * (p * vals[bj]) : (p > 0.f ? mult * vals[bj] : 0.f);
+}
+
+cudaError_t launch_volce_bwd_sparse(const float* prob, const int* idx, const float* validity, const float* gloss,
+                                    float* vals, float* dots, int B, int J, long long nvox, cudaStream_t st) {
+  const int BJ = B * J;
+  k_ce_bwd_sparse<<<(BJ + 127) / 128, 128, 0, st>>>(prob, idx, validity, gloss, vals, dots, BJ, nvox);
+  return cudaGetLastError();
+}
+cudaError_t launch_softargmax_bwd_add_sparse(const float* prob, const int* idx, const float* vals, float* gvol, int B,
+                                             int J, long long nvox, int softmax, float mult, cudaStream_t st) {
+  const int BJ = B * J;
+  k_ce_add_sparse<<<(BJ + 127) / 128, 128, 0, st>>>(prob, idx, vals, gvol, BJ, nvox, softmax, mult);
+  return cudaGetLastError();
+}
+
 size_t volce_ws_bytes(int B, int J, long long nvox) {
   if (B <= 0 || J <= 0 || nvox <= 0) return 0;
   return (size_t)B * J * ce_chunks(nvox) * sizeof(DistIdx) + (size_t)B * J * sizeof(float);

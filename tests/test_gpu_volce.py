@@ -102,3 +102,43 @@ def test_chained_behind_the_soft_argmax():
         outs.append((total.item(), gv))
     assert abs(outs[0][0] - outs[1][0]) < 1e-4 * abs(outs[1][0])
     assert rel_err(outs[0][1], outs[1][1]) < 1e-4
+
+
+@pytest.mark.parametrize("softmax", [True, False])
+@pytest.mark.parametrize("with_dense", [False, True])
+def test_fused_soft_argmax_and_ce_equals_the_two_calls(softmax, with_dense):
+    """Same values and the same gradient as integrate + VolumetricCELoss chained through autograd, although the CE
+    gradient travels as B*J numbers (or is folded into a dense gradient when the caller also differentiates the
+    volumes output)."""
+    # (not the peaked generator with a multiplier here: for near-one-hot volumes the soft-argmax gradient at the peak is
+    #  ill-conditioned in fp32 -- the stock fp32 ops are ~1e-3 from fp64 there, see DESIGN.md -- and this test is about
+    #  the sparse/dense plumbing, which test_gpu_softargmax.py's tolerances would otherwise mask)
+    d = synthetic.make_softargmax_inputs(B=2, J=5, N=(12, 16, 20), seed=6, train=True, peaked=False)
+    coord = d["coord_volumes"].cuda()
+    gen = torch.Generator().manual_seed(14)
+    kp_gt = (coord.cpu().flatten(1, 3).mean(1, keepdim=True) + 300.0 * torch.randn(2, 5, 3, generator=gen)).cuda()
+    val = (torch.rand(2, 5, 1, generator=gen) > 0.3).float().cuda()
+    gcoords = torch.randn(2, 5, 3, generator=gen).cuda()
+    gdense = torch.randn(d["volumes"].shape, generator=gen).cuda() * 1e-3
+    vols = d["volumes"].abs() + 0.01 if not softmax else d["volumes"]      # relu mode: keep -log(p) finite
+
+    def run(fused):
+        vol = vols.cuda().requires_grad_(True)
+        if fused:
+            kp, prob, ce = lt_b200.integrate_tensor_3d_with_coordinates_and_ce(vol, coord, kp_gt, val, softmax,
+                                                                               multiplier=2.0)
+        else:
+            kp, prob = ref_ops.integrate_tensor_3d_with_coordinates(vol * 2.0, coord, softmax=softmax)
+            ce = ref_ops.volumetric_ce_loss(coord, prob, kp_gt, val)
+        outs, grads = [kp, ce], [gcoords, torch.tensor(0.7, device="cuda")]
+        if with_dense:
+            outs.append(prob); grads.append(gdense)
+        (gv,) = torch.autograd.grad(outs, vol, grads)
+        return kp.detach(), prob.detach(), ce.item(), gv
+
+    a, b = run(True), run(False)
+    # against stock fp32 ATen (bmm over N^3 terms; un-normalised relu sums reach 1e6): fp32-sum accuracy, not 1e-3 mm
+    assert (a[0] - b[0]).abs().max().item() < max(2e-2, 2e-5 * b[0].abs().max().item())
+    assert rel_err(a[1], b[1]) < 1e-5
+    assert abs(a[2] - b[2]) <= 1e-5 * abs(b[2])
+    assert rel_err(a[3], b[3]) < 1e-4
