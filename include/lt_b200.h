@@ -8,6 +8,7 @@
  *   lt_softargmax_*  replaces  mvn/utils/op.py:84-96      integrate_tensor_3d_with_coordinates
  *   lt_softargmax2d_* replaces mvn/utils/op.py:11-47      integrate_tensor_2d
  *   lt_volce_*        replaces mvn/models/loss.py:52-80   VolumetricCELoss.forward
+ *   lt_coord_volumes  replaces mvn/models/triangulation.py:306-341  (coordinate-volume construction)
  *   lt_dlt_*         replaces  mvn/utils/multiview.py:132-174  triangulate_batch_of_points /
  *                                                              triangulate_point_from_multiple_views_linear_torch
  *
@@ -123,6 +124,15 @@ int lt_softargmax2d_fwd(const float *hm, float *coords, float *prob, int BJ, int
 int lt_softargmax2d_bwd(const float *prob, const float *coords, const float *grad_coords,
                         const float *grad_prob, float *grad_hm, int BJ, int H, int W, int softmax,
                         float multiplier, void *stream);
+
+/* ---- K6: coordinate volumes  (mvn/models/triangulation.py:306-341, mvn/utils/volumetric.py:87-114) ----
+ * spec (B, LT_COORD_SPEC) fp32 per item: pos[3] (cuboid corner), step[3] (side/(N-1)), centre[3] (base point),
+ * rot[9] (row-major rotation about the base point).  out (B,N0,N1,N2,3):
+ *   out[b,i0,i1,i2,:] = rot * ((pos + step*(i0,i1,i2)) - centre) + centre   in the reference's fp32 operation order.
+ * transfer=1 applies the CMU->Human3.6M swap of triangulation.py:336-339: out[i0,i1,i2] = cv[i0,i2,N1-1-i1]. */
+#define LT_COORD_SPEC 18
+int lt_coord_volumes(const float *spec, float *out, int B, int N0, int N1, int N2, int transfer,
+                     void *stream);
 
 /* ---- K5: volumetric cross-entropy loss  (mvn/models/loss.py:52-80 VolumetricCELoss) --------------
  * coord (B,nvox,3)  prob (B,J,nvox) = second output of lt_softargmax_fwd  kp_gt (B,J,3)  validity (B,J)

@@ -39,6 +39,7 @@ SIGNATURES = {
     "lt_softargmax_bwd": (_i, [_vp] * 7 + [_i, _i, _ll, _i, _f, _vp]),
     "lt_softargmax2d_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _f, _vp]),
     "lt_softargmax2d_bwd": (_i, [_vp] * 5 + [_i, _i, _i, _i, _f, _vp]),
+    "lt_coord_volumes": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "lt_volce_ws_bytes": (ctypes.c_size_t, [_i, _i, _ll]),
     "lt_volce_fwd": (_i, [_vp] * 7 + [_i, _i, _ll, _vp]),
     "lt_volce_bwd": (_i, [_vp] * 5 + [_i, _i, _ll, _vp]),

@@ -178,6 +178,15 @@ LT_API int lt_softargmax2d_bwd(const float* prob, const float* coords, const flo
                                                       softmax ? 1 : 0, multiplier, as_stream(stream)));
 }
 
+LT_API int lt_coord_volumes(const float* spec, float* out, int B, int N0, int N1, int N2, int transfer, void* stream) {
+  LT_REQUIRE(B >= 0 && N0 >= 0 && N1 >= 0 && N2 >= 0, "negative extent");
+  LT_REQUIRE(B <= 65535, "B > 65535");
+  LT_REQUIRE(!transfer || N1 == N2, "the CMU->Human3.6M axis swap needs N1 == N2 (triangulation.py:337)");
+  if ((long long)B * N0 * N1 * N2 == 0) return 0;
+  LT_REQUIRE(spec && out, "null pointer");
+  return finish(__func__, lt::launch_coord_volumes(spec, out, B, N0, N1, N2, transfer ? 1 : 0, as_stream(stream)));
+}
+
 LT_API size_t lt_volce_ws_bytes(int B, int J, long long nvox) { return lt::volce_ws_bytes(B, J, nvox); }
 
 LT_API int lt_volce_fwd(const float* coord, const float* prob, const float* kp_gt, const float* validity, float* loss,

@@ -37,6 +37,8 @@ cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const f
                                   float* grad_vol, int B, int J, long long nvox, int softmax, float mult,
                                   cudaStream_t st);
 
+cudaError_t launch_coord_volumes(const float* spec, float* out, int B, int N0, int N1, int N2, int transfer,
+                                 cudaStream_t st);
 size_t volce_ws_bytes(int B, int J, long long nvox);
 cudaError_t launch_volce_fwd(const float* coord, const float* prob, const float* kp, const float* validity, float* loss,
                              int* idx_out, void* ws, int B, int J, long long nvox, cudaStream_t st);

@@ -1,0 +1,69 @@
+"""Coordinate volumes for the volumetric net: the block of ``VolumetricTriangulationNet.forward`` that builds
+``coord_volumes`` (reference ``mvn/models/triangulation.py:280-341`` with ``mvn/utils/volumetric.py:87-114``) as ONE
+launch for the whole batch instead of a python loop of ~20 small ops per item. CUDA only.
+
+The reference does this inline, so there is no function to mirror; the arguments are the quantities that block reads:
+the per-item base point (pelvis), ``cuboid_side``, ``volume_size``, the rotation angle/axis and the
+``transfer_cmu_to_human36m`` flag.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .op import _stream
+
+COORD_SPEC = 18
+
+
+def rotation_matrix(axis, theta):
+    """Counter-clockwise rotation about ``axis`` by ``theta`` (Euler-Rodrigues), float64 like volumetric.py:87-100."""
+    axis = np.asarray(axis, dtype=np.float64)
+    axis = axis / np.sqrt(np.dot(axis, axis))
+    a = np.cos(theta / 2.0)
+    b, c, d = -axis * np.sin(theta / 2.0)
+    aa, bb, cc, dd = a * a, b * b, c * c, d * d
+    bc, ad, ac, ab, bd, cd = b * c, a * d, a * c, a * b, b * d, c * d
+    return np.array([[aa + bb - cc - dd, 2 * (bc + ad), 2 * (bd - ac)],
+                     [2 * (bc - ad), aa + cc - bb - dd, 2 * (cd + ab)],
+                     [2 * (bd + ac), 2 * (cd - ab), aa + dd - bb - cc]])
+
+
+def coord_volume_specs(base_points, cuboid_side, volume_size, thetas=None, axis=(0, 0, 1)):
+    """Host side: (B, 18) float32 = [position, step, centre, rotation] per item, each rounded to fp32 exactly where the
+    reference's torch ops round them (python/numpy scalars become fp32 operands of fp32 tensor ops)."""
+    base_points = np.asarray(base_points, dtype=np.float64).reshape(-1, 3)
+    B = base_points.shape[0]
+    sizes = np.broadcast_to(np.asarray(volume_size, dtype=np.int64), (3,))
+    thetas = np.zeros(B) if thetas is None else np.broadcast_to(np.asarray(thetas, dtype=np.float64), (B,))
+    sides = np.array([cuboid_side] * 3, dtype=np.float64)                # triangulation.py:298
+    spec = np.zeros((B, COORD_SPEC), dtype=np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        step = sides / (sizes - 1)                                       # triangulation.py:311-313
+    for b in range(B):
+        spec[b, 0:3] = base_points[b] - sides / 2                        # triangulation.py:299
+        spec[b, 3:6] = step
+        spec[b, 6:9] = base_points[b]                                    # triangulation.py:328
+        spec[b, 9:18] = rotation_matrix(axis, thetas[b]).reshape(-1)     # volumetric.py:106-107
+    return torch.from_numpy(spec)
+
+
+def build_coord_volumes(base_points, cuboid_side, volume_size, thetas=None, axis=(0, 0, 1),
+                        transfer_cmu_to_human36m=False, device="cuda"):
+    """(B, N0, N1, N2, 3) fp32 world coordinates of the voxel centres.
+
+    base_points (B,3) array-like (pelvis, mm); cuboid_side float (mm); volume_size int or (N0,N1,N2); thetas None
+    (evaluation: 0.0, triangulation.py:320) or B angles (training: uniform in [0, 2pi), :318); axis (0,0,1) for
+    ``kind == 'mpii'``, (0,1,0) for ``'coco'`` (:322-325); transfer_cmu_to_human36m as in :336-339."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("lt_b200: build_coord_volumes only exists as a CUDA kernel (no CPU fallback)")
+    L = _lib.lib()
+    N0, N1, N2 = (int(v) for v in np.broadcast_to(np.asarray(volume_size, dtype=np.int64), (3,)))
+    spec = coord_volume_specs(base_points, cuboid_side, (N0, N1, N2), thetas, axis)
+    B = spec.shape[0]
+    with torch.cuda.device(device):
+        spec_d = spec.to(device, non_blocking=True)
+        out = torch.empty((B, N0, N1, N2, 3), device=device, dtype=torch.float32)
+        _lib.check(L.lt_coord_volumes(_lib.ptr(spec_d), _lib.ptr(out), B, N0, N1, N2,
+                                      1 if transfer_cmu_to_human36m else 0, _stream()))
+    return out

@@ -99,6 +99,39 @@ def run_softargmax2d(tag, softmax, B, J, H, W, seed, scale=1.0):
     npz("softargmax2d_%s" % tag, softmax=np.array(int(softmax)), **res)
 
 
+def run_coordvol(tag, n, seed, axis, transfer):
+    """The reference's own pieces where they are callable (Cuboid3D, rotate_coord_volume from mvn/utils/volumetric.py)
+    around the inline statements of triangulation.py:306-313,331-339, which only exist inside forward()."""
+    from mvn.utils import volumetric as ref_vol
+    rng = np.random.RandomState(seed)
+    B = 3
+    base = rng.normal(0.0, 300.0, size=(B, 3))
+    thetas = np.concatenate([[0.0], rng.uniform(0.0, 2 * np.pi, size=B - 1)])
+    side = 2500.0
+    vols = []
+    for b in range(B):
+        sides = np.array([side, side, side])
+        position = base[b] - sides / 2
+        ref_vol.Cuboid3D(position, sides)
+        xxx, yyy, zzz = torch.meshgrid(torch.arange(n), torch.arange(n), torch.arange(n))
+        grid = torch.stack([xxx, yyy, zzz], dim=-1).type(torch.float).reshape((-1, 3))
+        gc = torch.zeros_like(grid)
+        gc[:, 0] = position[0] + (sides[0] / (n - 1)) * grid[:, 0]
+        gc[:, 1] = position[1] + (sides[1] / (n - 1)) * grid[:, 1]
+        gc[:, 2] = position[2] + (sides[2] / (n - 1)) * grid[:, 2]
+        cv = gc.reshape(n, n, n, 3)
+        center = torch.from_numpy(base[b]).type(torch.float)
+        cv = cv - center
+        cv = ref_vol.rotate_coord_volume(cv, thetas[b], axis)
+        cv = cv + center
+        if transfer:
+            cv = cv.permute(0, 2, 1, 3)
+            cv = cv.index_select(1, torch.arange(cv.shape[1] - 1, -1, -1).long())
+        vols.append(cv)
+    npz("coordvol_%s" % tag, base_points=base, thetas=thetas, axis=np.array(axis), side=np.array(side),
+        volume_size=np.array(n), transfer=np.array(int(transfer)), coord_volumes=torch.stack(vols))
+
+
 def run_volce(tag, B, J, N, seed, spread):
     """The unmodified VolumetricCELoss (mvn/models/loss.py:52-80) on the softmaxed volumes of the unmodified
     integrate_tensor_3d_with_coordinates; ground-truth joints = predicted joints + N(0, spread mm)."""
@@ -182,6 +215,9 @@ def main():
     run_softargmax2d("small_softmax", True, B=2, J=3, H=7, W=9, seed=41)
     run_softargmax2d("small_relu", False, B=2, J=3, H=7, W=9, seed=42)
     run_softargmax2d("sharp_softmax", True, B=1, J=4, H=24, W=24, seed=43, scale=100.0)   # heatmap_multiplier = 100
+    run_coordvol("mpii", 8, 61, [0, 0, 1], False)
+    run_coordvol("coco", 6, 62, [0, 1, 0], False)
+    run_coordvol("cmu_transfer", 8, 63, [0, 0, 1], True)
     run_volce("small", B=2, J=3, N=(5, 6, 7), seed=51, spread=150.0)
     run_volce("cube12", B=2, J=4, N=12, seed=52, spread=60.0)
     run_dlt("conf", B=3, V=4, J=5, seed=31)

@@ -102,3 +102,20 @@ def test_patch_reference_swaps_the_three_call_sites():
         assert ref_loss.VolumetricCELoss is not lt_b200.loss.VolumetricCELoss
     finally:
         sys.path.remove("/root/reference")
+
+
+def test_coord_volume_specs_round_like_the_reference():
+    """position/step/centre/rotation are rounded to fp32 where the reference's torch ops round their python scalars"""
+    import numpy as np
+    from lt_b200 import volumetric
+    base = np.array([[10.123456789, -20.5, 1000.000123]])
+    spec = volumetric.coord_volume_specs(base, 2500.0, 64, thetas=[0.3], axis=(0, 0, 1))
+    assert spec.shape == (1, 18) and spec.dtype == torch.float32
+    assert np.array_equal(spec[0, 0:3].numpy(), (base[0] - 1250.0).astype(np.float32))
+    assert np.array_equal(spec[0, 3:6].numpy(), np.full(3, 2500.0 / 63).astype(np.float32))
+    assert np.array_equal(spec[0, 6:9].numpy(), base[0].astype(np.float32))
+    R = spec[0, 9:].view(3, 3).double().numpy()
+    assert np.allclose(R @ R.T, np.eye(3), atol=1e-6) and np.allclose(R[2], [0, 0, 1], atol=1e-7)
+    assert np.isclose(R[0, 0], np.cos(0.3), atol=1e-7)
+    with pytest.raises(RuntimeError):
+        volumetric.build_coord_volumes(base, 2500.0, 8, device="cpu")

@@ -86,6 +86,19 @@ def test_softargmax2d_matches_reference(name):
     assert torch.allclose(c64, g["coords64"], rtol=1e-12, atol=1e-12) and torch.allclose(p64, g["prob64"], rtol=1e-12, atol=1e-15)
 
 
+@pytest.mark.parametrize("name", golden_names("coordvol_"))
+def test_coord_volume_matches_reference(name):
+    g = load_golden(name)
+    for b in range(g["base_points"].shape[0]):
+        cv = ref_ops.build_coord_volume(g["base_points"][b].numpy(), g["side"], g["volume_size"], g["thetas"][b].item(),
+                                        g["axis"].tolist(), bool(g["transfer"]))
+        assert torch.equal(cv, g["coord_volumes"][b])          # same statements on the same BLAS: same bits
+    # theta = 0 keeps the grid axis-aligned: item 0 spans exactly [base - side/2, base + side/2] per axis
+    cv0 = g["coord_volumes"][0]
+    lo, hi = cv0.flatten(0, 2).min(0).values.double(), cv0.flatten(0, 2).max(0).values.double()
+    assert torch.allclose((lo + hi) / 2, g["base_points"][0], atol=1e-3) and torch.allclose(hi - lo, torch.full((3,), g["side"], dtype=torch.float64), atol=1e-3)
+
+
 @pytest.mark.parametrize("name", golden_names("volce_"))
 def test_volumetric_ce_matches_reference(name):
     g = load_golden(name)
