@@ -7,7 +7,9 @@ path on synthetic Human3.6M-shaped data (BASELINE.json metric).
 One "step" = one pass of the hot path over one batch: K0 (layout) + K1 fwd + K2 fwd + K2 bwd + K1 bwd + K0 inverse.
 `value`  : device-resident arm, direct C-ABI launches on preallocated buffers, CUDA events, max over ranks.
 `e2e`    : the public python API (lt_b200.unproject_heatmaps / integrate_tensor_3d_with_coordinates under autograd) fed
-           from PINNED HOST tensors every step (H2D inside the timed region) with the loss + coordinates read back.
+           from PINNED HOST tensors every step (H2D inside the timed region: feature maps, projection matrices and the
+           cuboid specs; the coordinate volumes are built on the device like the reference does) with the loss +
+           coordinates read back.
 `roofline`: per-kernel CUDA-event durations taken inside the same timed loop against MEASURED_PEAKS.json.
 `cpu_baseline`: the oracle port of the reference's torch CPU path, timed on this box's host cores (rank 0, N=1).
 --impl reference prints the same line for the CPU reference arm (oracle port; the reference is pure python and its
@@ -25,6 +27,12 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+
+# ceilings of the two access patterns K1 is made of, measured in isolation on this pool's B200
+# (tools/microbench/red_paths.cu, profiles/r1c_microbench_red_paths.txt): fp32 reduction payload the L2 retires per
+# second (the same whether issued as red.global.add.v4.f32 or as TMA bulk reduce), and LDG.128 tap-gather bytes.
+L2_RED_PEAK_GBS = 6352.0
+L1_GATHER_PEAK_GBS = 18537.0
 
 WORKLOADS = {
     # name: B per GPU (weak) or total (strong), V, C, H, W, N, J, aggregation, scaling
@@ -148,10 +156,17 @@ class DeviceStep:
         self.gfeat_hwc = torch.empty_like(self.feat_hwc)
         self.gfeat = torch.empty_like(self.feat)
         self.gconf = torch.empty_like(self.conf) if conf else None
+        self.Cp = self.L.lt_padded_channels(w["C"])
         ws_bytes = max(self.L.lt_softargmax_ws_bytes(B, w["J"], nvox),
                        self.L.lt_unproject_bwd_ws_bytes(B, w["V"], w["C"], *self.N), 4)
         self.ws = torch.empty((ws_bytes // 4,), device=dev)
         self.agg = {"sum": 0, "conf": 1, "max": 2, "softmax": 3}[w["agg"]]
+
+    def valid_voxel_views(self):
+        try:
+            return _valid_voxel_views(self.coord, self.proj, self.w["H"], self.w["W"])
+        except Exception:
+            return None
 
     def run(self, events=None):
         L, p, chk, w, B = self.L, self.lib.ptr, self.lib.check, self.w, self.B
@@ -193,9 +208,30 @@ class DeviceStep:
         mark(6)
 
 
+def _valid_voxel_views(coord, proj, H, W):
+    """Number of (voxel, view) pairs with at least one bilinear tap inside the image: op.py:117-130 + the unnormalise
+    step of grid_sample (align_corners=False), evaluated with torch ops once at set-up (not timed)."""
+    B = coord.shape[0]
+    total = 0
+    for b in range(B):
+        pts = torch.cat([coord[b].reshape(-1, 3), torch.ones(coord[b].numel() // 3, 1, device=coord.device)], dim=1)
+        for v in range(proj.shape[1]):
+            p = pts @ proj[b, v].t()
+            z = p[:, 2]
+            ix = ((2.0 * (p[:, 0] / z / H - 0.5) + 1.0) * W - 1.0) * 0.5
+            iy = ((2.0 * (p[:, 1] / z / W - 0.5) + 1.0) * H - 1.0) * 0.5
+            total += int(((z > 0) & (ix > -1) & (ix < W) & (iy > -1) & (iy < H)).sum().item())
+    return total
+
+
 class E2EStep:
-    """Public-API arm: pinned host inputs -> H2D -> unproject -> (V2V stand-in: first J channels) -> soft-argmax ->
-    L1 loss -> backward -> loss + coordinates back to the host.
+    """Public-API arm: pinned host inputs -> H2D -> coordinate volumes -> unproject (+ its backward) and soft-argmax
+    -> L1 loss (+ its backward) -> loss + coordinates back to the host. The same work as one step of the device arm.
+
+    The host inputs are what the reference's forward receives from its data loader: feature maps, projection
+    matrices and the cuboid of every item (base point, side, rotation: 18 floats). Like the reference
+    (triangulation.py:280-341 builds `coord_volumes` on the device), the coordinate volumes are made on the device
+    every step (lt_b200.volumetric.coord_volumes_from_specs), not shipped over PCIe.
 
     Every step copies ITS OWN inputs from pinned host memory inside the timed region. Like a DataLoader with
     pin_memory + non_blocking prefetch, the copy of step i+1 is issued on a second stream while step i computes
@@ -205,7 +241,11 @@ class E2EStep:
     def __init__(self, dstep):
         h, w = dstep.host, dstep.w
         self.w, self.dev = w, dstep.dev
-        host = {"feat": h["heatmaps"], "proj": h["proj_matricies"], "coord": h["coord_volumes"],
+        self.x, self.gvol = dstep.x, dstep.gvol
+        from lt_b200 import volumetric
+        self.vol_size = tuple(h["coord_volumes"].shape[1:4])   # (N0/ranks, N, N) for the slab-sharded cfg5
+        specs = volumetric.coord_volume_specs(h["base_points"], 2500.0, self.vol_size, h["thetas"])
+        host = {"feat": h["heatmaps"], "proj": h["proj_matricies"], "spec": specs,
                 "target": torch.zeros(dstep.B, w["J"], 3)}
         if h["vol_confidences"] is not None:
             host["conf"] = h["vol_confidences"]
@@ -248,11 +288,14 @@ class E2EStep:
         cur.wait_event(self.copied[k])
         d = self.dbuf[k]
         feat = d["feat"].detach().requires_grad_(True)
-        vol = lt_b200.unproject_heatmaps(feat, d["proj"], d["coord"], w["agg"], d.get("conf"))
-        x = vol[:, :w["J"]]                     # stand-in for the V2V net (stays in PyTorch, out of scope)
-        coords, _ = lt_b200.integrate_tensor_3d_with_coordinates(x, d["coord"], softmax=True)
+        coord = lt_b200.volumetric.coord_volumes_from_specs(d["spec"], self.vol_size)
+        vol = lt_b200.unproject_heatmaps(feat, d["proj"], coord, w["agg"], d.get("conf"))
+        # The V2V net between the two ops stays in PyTorch and is out of scope: as in the device arm and the CPU arm,
+        # its output (x) and the gradient it sends back into the unprojected volume (gvol) are device-resident tensors.
+        x = self.x.detach().requires_grad_(True)
+        coords, _ = lt_b200.integrate_tensor_3d_with_coordinates(x, coord, softmax=True)
         loss = (coords - d["target"]).abs().mean()
-        loss.backward()
+        torch.autograd.backward([loss, vol], [None, self.gvol])
         self.h_loss.copy_(loss.detach().view(1), non_blocking=True)
         self.h_coords.copy_(coords.detach(), non_blocking=True)
         self.consumed[k].record(cur)
@@ -413,6 +456,19 @@ def main():
                 "whole_step": {"achieved": round(path_gbs, 1), "frac": round(path_gbs / peak, 4),
                                "note": "algorithmic bytes of K1 fwd/bwd + K2 fwd/bwd over the whole step time"},
                 "kernels": kernels}
+    # What actually binds K1 on this chip is not HBM: the backward's scatter is limited by the L2
+    # reduction units, the forward's gather by the L1 data pipe. Both ceilings were measured with the same address
+    # pattern in isolation (tools/microbench/red_paths.cu -> profiles/r1c_microbench_red_paths.txt).
+    taps = step.valid_voxel_views()
+    if taps is not None:
+        tap_bytes = taps * 4 * step.Cp * 4          # 4 bilinear taps x Cp channels x fp32 per valid (voxel, view)
+        for name, key, kind, pk in (("k1_unproject_bwd", "scatter", "l2_reduction_units", L2_RED_PEAK_GBS),
+                                    ("k1_unproject_fwd", "gather", "l1_gather", L1_GATHER_PEAK_GBS)):
+            ach = tap_bytes / (kernels[name]["ms"] * 1e-3) / 1e9
+            kernels[name]["binding_limit"] = {"kind": kind, "payload_bytes": tap_bytes, "achieved": round(ach, 1),
+                                              "peak": pk, "unit": "GB/s", "frac": round(ach / pk, 4),
+                                              "peak_source": "microbenchmark, profiles/r1c_microbench_red_paths.txt"}
+        roofline["binding_limit"] = kernels[top].get("binding_limit")
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
@@ -427,8 +483,10 @@ def main():
         ems, _, _ = timed(lambda e: es.run(), e_steps, 3, False, after_warmup=es.drain)
         e2e = {"value": total_B * e_steps / (ems * 1e-3), "unit": "volumes/s", "h2d_bytes_per_step": es.h2d,
                "d2h_bytes_per_step": es.d2h, "steps": e_steps, "ms_per_step": ems / e_steps,
-               "note": "public python ops under autograd; pinned-host inputs copied every step on a second stream "
-                       "(prefetch depth 1), loss + coordinates read back every step"}
+               "note": "public python ops under autograd; pinned-host inputs (feature maps, projection matrices, "
+                       "18-float cuboid specs) copied every step on a second stream (prefetch depth 1), coordinate "
+                       "volumes built on the device as triangulation.py:280-341 does, loss + coordinates read back "
+                       "every step"}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

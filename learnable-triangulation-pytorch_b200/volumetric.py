@@ -47,6 +47,24 @@ def coord_volume_specs(base_points, cuboid_side, volume_size, thetas=None, axis=
     return torch.from_numpy(spec)
 
 
+def coord_volumes_from_specs(specs, volume_size, transfer_cmu_to_human36m=False):
+    """The launch on its own: ``specs`` (B,18) fp32 ALREADY ON THE DEVICE (``coord_volume_specs`` + a pinned,
+    non-blocking copy in a data-loading pipeline) -> (B,N0,N1,N2,3). No host work, no synchronisation."""
+    if not (torch.is_tensor(specs) and specs.is_cuda):
+        raise RuntimeError("lt_b200: specs must be a CUDA tensor (no CPU fallback)")
+    if specs.dim() != 2 or specs.shape[1] != COORD_SPEC:
+        raise RuntimeError("specs must be (B, {}), got {}".format(COORD_SPEC, tuple(specs.shape)))
+    L = _lib.lib()
+    N0, N1, N2 = (int(v) for v in np.broadcast_to(np.asarray(volume_size, dtype=np.int64), (3,)))
+    B = specs.shape[0]
+    with torch.cuda.device(specs.device):
+        spec_d = specs.detach().to(torch.float32).contiguous()
+        out = torch.empty((B, N0, N1, N2, 3), device=specs.device, dtype=torch.float32)
+        _lib.check(L.lt_coord_volumes(_lib.ptr(spec_d), _lib.ptr(out), B, N0, N1, N2,
+                                      1 if transfer_cmu_to_human36m else 0, _stream()))
+    return out
+
+
 def build_coord_volumes(base_points, cuboid_side, volume_size, thetas=None, axis=(0, 0, 1),
                         transfer_cmu_to_human36m=False, device="cuda"):
     """(B, N0, N1, N2, 3) fp32 world coordinates of the voxel centres.
@@ -57,13 +75,7 @@ def build_coord_volumes(base_points, cuboid_side, volume_size, thetas=None, axis
     device = torch.device(device)
     if device.type != "cuda":
         raise RuntimeError("lt_b200: build_coord_volumes only exists as a CUDA kernel (no CPU fallback)")
-    L = _lib.lib()
     N0, N1, N2 = (int(v) for v in np.broadcast_to(np.asarray(volume_size, dtype=np.int64), (3,)))
     spec = coord_volume_specs(base_points, cuboid_side, (N0, N1, N2), thetas, axis)
-    B = spec.shape[0]
     with torch.cuda.device(device):
-        spec_d = spec.to(device, non_blocking=True)
-        out = torch.empty((B, N0, N1, N2, 3), device=device, dtype=torch.float32)
-        _lib.check(L.lt_coord_volumes(_lib.ptr(spec_d), _lib.ptr(out), B, N0, N1, N2,
-                                      1 if transfer_cmu_to_human36m else 0, _stream()))
-    return out
+        return coord_volumes_from_specs(spec.to(device, non_blocking=True), (N0, N1, N2), transfer_cmu_to_human36m)
