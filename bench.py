@@ -260,6 +260,7 @@ class E2EStep:
         self.d2h = (self.h_loss.numel() + self.h_coords.numel()) * 4
         self.issued = 0   # copies issued so far
         self.done = 0     # steps computed so far
+        self.graphs = None
 
     def _issue_copy(self):
         k = self.issued % 2
@@ -277,16 +278,10 @@ class E2EStep:
         torch.cuda.synchronize()
         self.done = self.issued
 
-    def run(self):
+    def _compute(self, k):
+        """The step on input set k: the user-facing calls, nothing else."""
         import lt_b200
-        w = self.w
-        if self.issued == self.done:      # nothing in flight (first step): this step's own copy
-            self._issue_copy()
-        self._issue_copy()                # prefetch the next step's inputs while this one computes
-        k = self.done % 2
-        cur = torch.cuda.current_stream()
-        cur.wait_event(self.copied[k])
-        d = self.dbuf[k]
+        w, d = self.w, self.dbuf[k]
         feat = d["feat"].detach().requires_grad_(True)
         coord = lt_b200.volumetric.coord_volumes_from_specs(d["spec"], self.vol_size)
         vol = lt_b200.unproject_heatmaps(feat, d["proj"], coord, w["agg"], d.get("conf"))
@@ -298,9 +293,52 @@ class E2EStep:
         torch.autograd.backward([loss, vol], [None, self.gvol])
         self.h_loss.copy_(loss.detach().view(1), non_blocking=True)
         self.h_coords.copy_(coords.detach(), non_blocking=True)
+        return feat.grad
+
+    def capture(self):
+        """Capture the step once per input set into a CUDA graph (the ops enqueue on torch's current stream, allocate
+        through torch's caching allocator and never synchronise, so `torch.cuda.graph` can record them, autograd
+        included). Falls back to eager launches when capture is refused; `self.graphs` says which one ran."""
+        self.graphs = None
+        try:
+            cur = torch.cuda.current_stream()
+            side = torch.cuda.Stream(device=self.dev)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):          # warm-up off the default stream, as torch.cuda.graph requires
+                for k in range(2):
+                    self.dbuf[k]["feat"].normal_()
+                    for name in ("proj", "spec"):
+                        self.dbuf[k][name].copy_(self.host[name], non_blocking=True)
+                    self._compute(k)
+            cur.wait_stream(side)
+            torch.cuda.synchronize()
+            graphs = []
+            for k in range(2):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._compute(k)
+                graphs.append(g)
+            torch.cuda.synchronize()
+            self.graphs = graphs
+        except Exception as e:  # noqa: BLE001
+            sys.stderr.write("e2e: CUDA-graph capture refused (%s: %s); running the ops eagerly\n" % (type(e).__name__, e))
+            torch.cuda.synchronize()
+            self.graphs = None
+        return self.graphs is not None
+
+    def run(self):
+        if self.issued == self.done:      # nothing in flight (first step): this step's own copy
+            self._issue_copy()
+        self._issue_copy()                # prefetch the next step's inputs while this one computes
+        k = self.done % 2
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self.copied[k])
+        if self.graphs is not None:
+            self.graphs[k].replay()
+        else:
+            self._compute(k)
         self.consumed[k].record(cur)
         self.done += 1
-        return feat.grad
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -351,6 +389,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded CPU sample (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer arm (profiling runs)")
+    ap.add_argument("--no-graph", action="store_true", help="e2e arm: launch the python ops eagerly instead of replaying "
+                                                            "a CUDA graph captured from them")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))
@@ -479,11 +519,13 @@ def main():
     e2e = None
     if not args.no_e2e:
         es = E2EStep(step)
+        graphed = (not args.no_graph) and es.capture()
         e_steps = max(3, min(args.steps, 50))
         ems, _, _ = timed(lambda e: es.run(), e_steps, 3, False, after_warmup=es.drain)
         e2e = {"value": total_B * e_steps / (ems * 1e-3), "unit": "volumes/s", "h2d_bytes_per_step": es.h2d,
-               "d2h_bytes_per_step": es.d2h, "steps": e_steps, "ms_per_step": ems / e_steps,
-               "note": "public python ops under autograd; pinned-host inputs (feature maps, projection matrices, "
+               "d2h_bytes_per_step": es.d2h, "steps": e_steps, "ms_per_step": ems / e_steps, "cuda_graph": graphed,
+               "note": "public python ops under autograd (captured once into a CUDA graph per input set when cuda_graph is "
+                       "true, replayed every step); pinned-host inputs (feature maps, projection matrices, "
                        "18-float cuboid specs) copied every step on a second stream (prefetch depth 1), coordinate "
                        "volumes built on the device as triangulation.py:280-341 does, loss + coordinates read back "
                        "every step"}

@@ -10,7 +10,8 @@ import subprocess
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblt_b200.so")
+# LT_B200_LIB: developer knob for A/B-ing differently built libraries on the GPU box (tools/gpu_variants.sh)
+LIB_PATH = os.environ.get("LT_B200_LIB") or os.path.join(_HERE, "liblt_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
 _c_float_p = ctypes.c_void_p  # device pointers travel as integers

@@ -28,8 +28,11 @@ __device__ __forceinline__ float softmax_mix4(float s0, float s1, float s2, floa
 // AGG: lt_agg.  ALIGNED: N2 % 8 == 0 so every run is a whole, 32-byte aligned sector.
 // kAggSoftmax is only launched here for V <= kViewChunk (all samples of a voxel in registers); more views go to
 // k_unproject_fwd_softmax_manyviews below.
+#ifndef LT_K1F_CTAS
+#define LT_K1F_CTAS 4
+#endif
 template <int LPV, int AGG, bool ALIGNED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 4) k_unproject_fwd(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fwd(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
