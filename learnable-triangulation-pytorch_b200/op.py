@@ -52,7 +52,7 @@ class _Unproject(torch.autograd.Function):
             hm = _f32c(heatmaps)
             proj_c, coord_c = _f32c(proj), _f32c(coord)
             conf_c = _f32c(conf) if conf is not None else None
-            # K0: gather layout (16-channel groups, zero border) of the feature maps; opaque to this side
+            # K0: gather layout (channels-last, padded channels, zero border) of the feature maps; opaque to this side
             feat = torch.empty((L.lt_feat_layout_elems(B * V, C, H, W),), device=hm.device, dtype=torch.float32)
             _lib.check(L.lt_feat_to_hwc(_lib.ptr(hm), _lib.ptr(feat), B * V, C, H, W, st))
             out = torch.empty((B, C, N0, N1, N2), device=hm.device, dtype=torch.float32)
