@@ -16,16 +16,15 @@ COORD_SPEC = 18
 
 
 def rotation_matrix(axis, theta):
-    """Counter-clockwise rotation about ``axis`` by ``theta`` (Euler-Rodrigues), float64 like volumetric.py:87-100."""
-    axis = np.asarray(axis, dtype=np.float64)
-    axis = axis / np.sqrt(np.dot(axis, axis))
-    a = np.cos(theta / 2.0)
-    b, c, d = -axis * np.sin(theta / 2.0)
-    aa, bb, cc, dd = a * a, b * b, c * c, d * d
-    bc, ad, ac, ab, bd, cd = b * c, a * d, a * c, a * b, b * d, c * d
-    return np.array([[aa + bb - cc - dd, 2 * (bc + ad), 2 * (bd - ac)],
-                     [2 * (bc - ad), aa + cc - bb - dd, 2 * (cd + ab)],
-                     [2 * (bd + ac), 2 * (cd - ab), aa + dd - bb - cc]])
+    """Rotation by ``theta`` about ``axis`` as the reference defines it (volumetric.py:87-100, Euler-Rodrigues with
+    the unit quaternion q = (cos(theta/2), -axis*sin(theta/2))), written in closed form:
+    R = (w^2 - |v|^2) I + 2 v v^T - 2 w [v]_x   for q = (w, v). float64."""
+    n = np.asarray(axis, dtype=np.float64)
+    n = n / np.linalg.norm(n)
+    w = np.cos(0.5 * theta)
+    v = -np.sin(0.5 * theta) * n
+    cross = np.array([[0.0, -v[2], v[1]], [v[2], 0.0, -v[0]], [-v[1], v[0], 0.0]])
+    return (w * w - v.dot(v)) * np.eye(3) + 2.0 * np.outer(v, v) - 2.0 * w * cross
 
 
 def coord_volume_specs(base_points, cuboid_side, volume_size, thetas=None, axis=(0, 0, 1)):
