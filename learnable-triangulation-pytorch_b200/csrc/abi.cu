@@ -182,6 +182,7 @@ LT_API int lt_coord_volumes(const float* spec, float* out, int B, int N0, int N1
   LT_REQUIRE(B >= 0 && N0 >= 0 && N1 >= 0 && N2 >= 0, "negative extent");
   LT_REQUIRE(B <= 65535, "B > 65535");
   LT_REQUIRE(!transfer || N1 == N2, "the CMU->Human3.6M axis swap needs N1 == N2 (triangulation.py:337)");
+  LT_REQUIRE((long long)N0 * N1 * N2 <= 0x7fffffffLL, "more than 2^31 voxels per item");
   if ((long long)B * N0 * N1 * N2 == 0) return 0;
   LT_REQUIRE(spec && out, "null pointer");
   return finish(__func__, lt::launch_coord_volumes(spec, out, B, N0, N1, N2, transfer ? 1 : 0, as_stream(stream)));

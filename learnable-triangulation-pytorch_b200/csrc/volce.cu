@@ -5,7 +5,7 @@
 // loop of B*J scalar gathers:   loss = sum_{b,j} validity[b,j] * -log(p[b,j,argmin_i |c_i - k_bj|] + 1e-6) / (B*J).
 // Here: one sweep over the coordinates (each voxel's xyz is fetched once and kept in registers for all J joints),
 // no temporary, no synchronisation.
-//   k_ce_argmin : grid (chunk, b). Per (joint, CTA) one (distance, voxel) pair, smallest distance first, smallest
+//   k_ce_argmin : grid (chunk, b). Per (joint, warp) one (distance, voxel) pair, smallest distance first, smallest
 //                 index among equal distances (torch.argmin returns the first minimum on CPU).
 //   k_ce_pick   : one warp per (b, j): merges the chunks, gathers p at the voxel, writes the term and the index.
 //   k_ce_sum    : one CTA: adds the B*J terms in the reference's order (b outer, j inner, fp32) and divides by B*J.
@@ -42,16 +42,20 @@ __device__ __forceinline__ DistIdx di_warp_min(DistIdx v) {
 
 static inline int ce_chunks(long long nvox) { return (int)((nvox + kCeChunk - 1) / kCeChunk); }
 
-// ws: [(b*J + j)][chunk] (dist, idx)
+// ws: [(b*J + j)][chunk * kCeWarps + warp] (dist, idx)
+// The square root of loss.py:66 is monotone, so the winner is found on the squared distances and only the voxels whose
+// square could round to the same root as the warp's smallest one (within 5e-7 relative: two fp32 numbers with the same
+// correctly rounded root differ by less than 2.4e-7) get an IEEE square root; among equal roots the lowest index wins,
+// exactly what argmin over the reference's sqrt'ed distances returns. Reductions are single REDUX instructions on the
+// bit patterns (non-negative floats order like unsigned integers); no shared memory, no barrier.
+constexpr int kCeWarps = kCeThreads / 32;
 __global__ void __launch_bounds__(kCeThreads) k_ce_argmin(const float* __restrict__ coord, const float* __restrict__ kp,
                                                           DistIdx* __restrict__ ws, int J, long long nvox) {
-  __shared__ DistIdx s_part[kCeThreads / 32];
   const int b = blockIdx.y, chunk = blockIdx.x, nchunk = gridDim.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long base = (long long)chunk * kCeChunk;
   const float* cb = coord + (size_t)b * nvox * 3;
-  // thread t owns voxels base + t*8 .. +7 (24 consecutive floats): indices increase with e, so a strict '<' keeps
-  // the first minimum
+  // thread t owns voxels base + t*8 .. +7 (24 consecutive floats)
   float cx[kCeEpt], cy[kCeEpt], cz[kCeEpt];
   const long long v0 = base + (long long)threadIdx.x * kCeEpt;
   if ((nvox & 3) == 0 && v0 + kCeEpt <= nvox) {  // 96 consecutive, 16-byte aligned bytes
@@ -73,27 +77,37 @@ __global__ void __launch_bounds__(kCeThreads) k_ce_argmin(const float* __restric
       cz[e] = in ? __ldg(cb + (v0 + e) * 3 + 2) : 0.f;
     }
   }
+  const int nin = (int)max(0LL, min((long long)kCeEpt, nvox - v0));  // voxels of this thread inside the volume
   for (int j = 0; j < J; ++j) {
     const float* k = kp + ((size_t)b * J + j) * 3;
     const float kx = __ldg(k), ky = __ldg(k + 1), kz = __ldg(k + 2);
-    DistIdx best = {INFINITY, 0x7fffffff};
+    float d2[kCeEpt];
+    float m2 = INFINITY;
 #pragma unroll
     for (int e = 0; e < kCeEpt; ++e) {
       const float dx = __fsub_rn(cx[e], kx), dy = __fsub_rn(cy[e], ky), dz = __fsub_rn(cz[e], kz);
-      const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-      const float d = __fsqrt_rn(d2);
-      if (v0 + e < nvox && d < best.d) { best.d = d; best.i = (int)(v0 + e); }
+      d2[e] = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+      if (e < nin) m2 = fminf(m2, d2[e]);       // NaN distances never win (coordinates are finite on this path)
     }
-    best = di_warp_min(best);
-    if (lane == 0) s_part[warp] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      DistIdx r = s_part[0];
+    const float wm2 = __uint_as_float(__reduce_min_sync(0xffffffffu, __float_as_uint(m2)));
+    const float thr = wm2 * 1.0000005f;
+    float bd = INFINITY;
+    unsigned bi = 0xffffffffu;
 #pragma unroll
-      for (int w = 1; w < kCeThreads / 32; ++w) r = di_min(r, s_part[w]);
-      ws[((size_t)b * J + j) * nchunk + chunk] = r;
+    for (int e = 0; e < kCeEpt; ++e) {
+      if (e < nin && d2[e] <= thr) {
+        const float d = __fsqrt_rn(d2[e]);
+        if (d < bd) { bd = d; bi = (unsigned)(v0 + e); }   // e ascending: strict '<' keeps the first
+      }
     }
-    __syncthreads();
+    const float wd = __uint_as_float(__reduce_min_sync(0xffffffffu, __float_as_uint(bd)));
+    const unsigned wi = __reduce_min_sync(0xffffffffu, bd == wd ? bi : 0xffffffffu);
+    if (lane == 0) {
+      DistIdx r;
+      r.d = wd;
+      r.i = wi == 0xffffffffu ? 0x7fffffff : (int)wi;
+      ws[((size_t)b * J + j) * nchunk * kCeWarps + (size_t)chunk * kCeWarps + warp] = r;
+    }
   }
 }
 
@@ -174,16 +188,16 @@ cudaError_t launch_softargmax_bwd_add_sparse(const float* prob, const int* idx, 
 
 size_t volce_ws_bytes(int B, int J, long long nvox) {
   if (B <= 0 || J <= 0 || nvox <= 0) return 0;
-  return (size_t)B * J * ce_chunks(nvox) * sizeof(DistIdx) + (size_t)B * J * sizeof(float);
+  return (size_t)B * J * ce_chunks(nvox) * kCeWarps * sizeof(DistIdx) + (size_t)B * J * sizeof(float);
 }
 
 cudaError_t launch_volce_fwd(const float* coord, const float* prob, const float* kp, const float* validity, float* loss,
                              int* idx_out, void* ws, int B, int J, long long nvox, cudaStream_t st) {
   const int nchunk = ce_chunks(nvox), BJ = B * J;
   DistIdx* parts = reinterpret_cast<DistIdx*>(ws);
-  float* terms = reinterpret_cast<float*>(parts + (size_t)BJ * nchunk);
+  float* terms = reinterpret_cast<float*>(parts + (size_t)BJ * nchunk * kCeWarps);
   k_ce_argmin<<<dim3((unsigned)nchunk, (unsigned)B), kCeThreads, 0, st>>>(coord, kp, parts, J, nvox);
-  k_ce_pick<<<BJ, 32, 0, st>>>(parts, prob, validity, terms, idx_out, nchunk, nvox);
+  k_ce_pick<<<BJ, 32, 0, st>>>(parts, prob, validity, terms, idx_out, nchunk * kCeWarps, nvox);
   k_ce_sum<<<1, 256, 0, st>>>(terms, loss, BJ);
   return cudaGetLastError();
 }

@@ -255,20 +255,22 @@ def integrate_tensor_2d(heatmaps, softmax=True):
 # --------------------------------------------------------------------------------------------------------------------
 # coordinate volumes  (reference: mvn/models/triangulation.py:306-341 + mvn/utils/volumetric.py:87-114)
 # --------------------------------------------------------------------------------------------------------------------
-def build_coord_volume(base_point, cuboid_side, volume_size, theta, axis, transfer_cmu_to_human36m=False):
+def build_coord_volume(base_point, cuboid_side, volume_size, theta, axis, transfer_cmu_to_human36m=False,
+                       device="cpu"):
     """One item, the same torch statements as the reference block: meshgrid -> position + step * index per axis
     (triangulation.py:306-313), minus centre, rot.mm(coord.t()).t(), plus centre (:331-333, volumetric.py:103-114),
     optional permute + reversed index_select (:336-339). base_point: float64 numpy (3,)."""
     n = volume_size
     sides = np.array([cuboid_side, cuboid_side, cuboid_side])
     position = base_point - sides / 2
-    xxx, yyy, zzz = torch.meshgrid(torch.arange(n), torch.arange(n), torch.arange(n), indexing="ij")
+    xxx, yyy, zzz = torch.meshgrid(torch.arange(n, device=device), torch.arange(n, device=device),
+                                   torch.arange(n, device=device), indexing="ij")
     grid = torch.stack([xxx, yyy, zzz], dim=-1).type(torch.float).reshape((-1, 3))
     grid_coord = torch.zeros_like(grid)
     for c in range(3):
         grid_coord[:, c] = position[c] + (sides[c] / (n - 1)) * grid[:, c]
     cv = grid_coord.reshape(n, n, n, 3)
-    center = torch.from_numpy(np.asarray(base_point)).type(torch.float)
+    center = torch.from_numpy(np.asarray(base_point)).type(torch.float).to(device)
     a = np.asarray(axis, dtype=np.float64)
     a = a / np.sqrt(np.dot(a, a))
     qa = np.cos(theta / 2.0)
@@ -276,13 +278,13 @@ def build_coord_volume(base_point, cuboid_side, volume_size, theta, axis, transf
     rot = np.array([[qa * qa + qb * qb - qc * qc - qd * qd, 2 * (qb * qc + qa * qd), 2 * (qb * qd - qa * qc)],
                     [2 * (qb * qc - qa * qd), qa * qa + qc * qc - qb * qb - qd * qd, 2 * (qc * qd + qa * qb)],
                     [2 * (qb * qd + qa * qc), 2 * (qc * qd - qa * qb), qa * qa + qd * qd - qb * qb - qc * qc]])
-    rot = torch.from_numpy(rot).type(torch.float)
+    rot = torch.from_numpy(rot).type(torch.float).to(device)
     cv = cv - center
     cv = rot.mm(cv.view(-1, 3).t()).t().view(n, n, n, 3)
     cv = cv + center
     if transfer_cmu_to_human36m:
         cv = cv.permute(0, 2, 1, 3)
-        cv = cv.index_select(1, torch.arange(cv.shape[1] - 1, -1, -1).long())
+        cv = cv.index_select(1, torch.arange(cv.shape[1] - 1, -1, -1).long().to(device))
     return cv.contiguous()
 
 
