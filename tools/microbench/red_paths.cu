@@ -37,6 +37,31 @@ __global__ void __launch_bounds__(256) k_red_v4(float* g, long long n) {
   }
 }
 
+// A': the same scatter as plain (non-atomic, racy) 16-byte stores: what the L2 write path takes without the reduction,
+//     and A'': as four scalar red.global.add.f32 per lane and tap instead of one v4.
+template <int MODE>
+__global__ void __launch_bounds__(256) k_scatter_other(float* g, long long n) {
+  const int lane = threadIdx.x & 31, grp = lane >> 3, q = lane & 7;
+  const long long warp = (blockIdx.x * 256LL + threadIdx.x) >> 5, nwarps = gridDim.x * 8LL;
+  for (long long i = warp * 4 + grp; i < n; i += nwarps * 4) {
+    int map, off; float4 w;
+    tap_of(i, map, off, w);
+    float* p = g + (size_t)map * Hp * Wp * Cp + off + q * 4;
+    const float wt[4] = {w.x, w.y, w.z, w.w};
+    const int d[4] = {0, Cp, Wp * Cp, Wp * Cp + Cp};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      if (MODE == 0) {
+        asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p + d[t]), "f"(wt[t]), "f"(wt[t] * 2), "f"(wt[t] * 3), "f"(wt[t] * 4) : "memory");
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p + d[t] + c), "f"(wt[t] * (c + 1)) : "memory");
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) k_red_bulk(float* g, long long n) {
   // per warp: 2 buffers x 4 voxels x 2 rows x 64 floats
   __shared__ __align__(128) float s_buf[8][2][4][2][64];
@@ -110,6 +135,22 @@ int main() {
       cudaMemcpy(h, g + (size_t)(5 * Wp + 7) * Cp, sizeof(h), cudaMemcpyDeviceToHost);
       printf("%s grid %5d: %.3f ms  %.1f GB/s payload  (err %s) probe %.4f %.4f %.4f %.4f\n", which ? "bulk-reduce" : "red.v4     ",
              grid, best, n * 512.0 / best * 1e-6, cudaGetErrorString(cudaGetLastError()), h[0], h[1], h[4], h[5]);
+    }
+  }
+  for (int mode = 0; mode < 2; ++mode) {
+    for (int grid : {148 * 8, 148 * 16}) {
+      float best = 1e9f;
+      for (int rep = 0; rep < 5; ++rep) {
+        cudaMemset(g, 0, elems * 4);
+        cudaEventRecord(a);
+        if (mode == 0) k_scatter_other<0><<<grid, 256>>>(g, n); else k_scatter_other<1><<<grid, 256>>>(g, n);
+        cudaEventRecord(b);
+        cudaEventSynchronize(b);
+        float ms; cudaEventElapsedTime(&ms, a, b);
+        if (ms < best) best = ms;
+      }
+      printf("%s grid %5d: %.3f ms  %.1f GB/s payload  (err %s)\n", mode ? "red.f32 x4 " : "st.v4 (racy)", grid, best,
+             n * 512.0 / best * 1e-6, cudaGetErrorString(cudaGetLastError()));
     }
   }
   float* out;
