@@ -108,6 +108,33 @@ __device__ __forceinline__ float warp_max(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
+// warp-wide maximum in ONE instruction: floats are mapped to integers with the same order (flip the magnitude bits of
+// negatives) and reduced with REDUX.MAX.S32. -inf stays the smallest value; NaNs are not expected on these paths.
+__device__ __forceinline__ float warp_max_redux(float v) {
+  int i = __float_as_int(v);
+  i ^= (i >> 31) & 0x7fffffff;
+  i = __reduce_max_sync(0xffffffffu, i);
+  i ^= (i >> 31) & 0x7fffffff;
+  return __int_as_float(i);
+}
+// Four sums across the warp with 6 shuffles instead of 20: the first two butterfly steps also halve the number of values
+// a lane carries (lanes with bit 4 clear keep a,b / set keep c,d; then bit 3 picks one of the pair). Every lane of the
+// lane octet k = lane >> 3 returns the warp-wide total of value k (a, b, c, d for k = 0..3). Fixed order: deterministic.
+__device__ __forceinline__ float warp_sum4(float a, float b, float c, float d) {
+  const int lane = threadIdx.x & 31;
+  const bool hi16 = lane & 16, hi8 = lane & 8;
+  float k0 = hi16 ? c : a, k1 = hi16 ? d : b;
+  const float s0 = hi16 ? a : c, s1 = hi16 ? b : d;
+  k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+  k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+  float k = hi8 ? k1 : k0;
+  const float s = hi8 ? k0 : k1;
+  k += __shfl_xor_sync(0xffffffffu, s, 8);
+  k += __shfl_xor_sync(0xffffffffu, k, 4);
+  k += __shfl_xor_sync(0xffffffffu, k, 2);
+  k += __shfl_xor_sync(0xffffffffu, k, 1);
+  return k;
+}
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

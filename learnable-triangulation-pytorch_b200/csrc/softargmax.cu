@@ -88,14 +88,14 @@ __global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __res
     }
   };
   auto reduce_row = [&](int j, const float (&x)[kSamEpt]) {
-    Lse5 r;
+    float tot, m_out;
     if (SOFTMAX) {
       // shift by the warp-wide max of the scaled logits (mult > 0 is guaranteed by the caller); padding
       // voxels carry -inf and contribute e = 0.
       float ms = -INFINITY;
 #pragma unroll
       for (int i = 0; i < kSamEpt; ++i) ms = fmaxf(ms, x[i] * mult);
-      const float wm = warp_max(ms);  // warp-wide shift: one rescale-free accumulation per warp
+      const float wm = warp_max_redux(ms);  // warp-wide shift: one rescale-free accumulation per warp
       float s = 0.f, sx = 0.f, sy = 0.f, sz = 0.f;
       if (wm > -INFINITY) {
         const float shift = -wm * kLog2e;
@@ -108,7 +108,8 @@ __global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __res
           sz = fmaf(e, cz[i], sz);
         }
       }
-      r = {wm, warp_sum(s), warp_sum(sx), warp_sum(sy), warp_sum(sz)};
+      tot = warp_sum4(s, sx, sy, sz);   // lane octet k holds the total of (S, Sx, Sy, Sz)[k]
+      m_out = wm;
     } else {
       float sx = 0.f, sy = 0.f, sz = 0.f;
 #pragma unroll
@@ -118,12 +119,12 @@ __global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __res
         sy = fmaf(e, cy[i], sy);
         sz = fmaf(e, cz[i], sz);
       }
-      r = {0.f, 1.f, warp_sum(sx), warp_sum(sy), warp_sum(sz)};
+      tot = warp_sum4(1.f / 32.f, sx, sy, sz);   // slot 1 of the tuple is the constant 1 (32 lanes x 1/32, exact)
+      m_out = 0.f;
     }
-    if (lane == 0) {
-      float* o = ws + (((size_t)b * J + j) * nchunk * kSamWarps + (size_t)chunk * kSamWarps + warp) * 5;
-      o[0] = r.m; o[1] = r.s; o[2] = r.x; o[3] = r.y; o[4] = r.z;
-    }
+    float* o = ws + (((size_t)b * J + j) * nchunk * kSamWarps + (size_t)chunk * kSamWarps + warp) * 5;
+    if ((lane & 7) == 0) o[1 + (lane >> 3)] = tot;
+    if (lane == 0) o[0] = m_out;
   };
   float xa[kSamEpt], xb[kSamEpt];
   if (J > 0) load_row(0, xa);
