@@ -8,6 +8,8 @@ Everything runs in hand-written sm_100a kernels behind the C ABI of ``include/lt
         reference: mvn/utils/op.py:84-96
     integrate_tensor_2d(heatmaps, softmax=True)
         reference: mvn/utils/op.py:11-47
+    integrate_tensor_3d(volumes, softmax=True)
+        reference: mvn/utils/op.py:50-81
 """
 import torch
 
@@ -204,6 +206,31 @@ def integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True, *
         volumes = volumes * multiplier
         multiplier = 1.0
     return _SoftArgmax.apply(volumes, coord_volumes, 1 if softmax else 0, multiplier)
+
+
+def integrate_tensor_3d(volumes, softmax=True):
+    """Soft-argmax of each joint volume in VOXEL-INDEX coordinates (reference: op.py:50-81; not used by the reference's
+    nets, kept so that every ``integrate_*`` of ``mvn.utils.op`` has its counterpart here).
+
+    volumes (B,J,N0,N1,N2). Returns ``(coordinates (B,J,3) as (x, y, z) indices, volumes)``: softmax=True gives the
+    softmax-normalised volume and its expected index; softmax=False gives relu(volumes) un-normalised while the
+    coordinates are divided by the total mass (op.py:73-76; 0/0 = nan as in the reference). Built from the same
+    kernels: the index grid is a coordinate volume with unit step (K6), the integration is K2."""
+    from . import volumetric
+    _require_cuda("volumes", volumes)
+    if volumes.dim() != 5:
+        raise ValueError("not enough values to unpack (expected 5, got {})".format(volumes.dim())
+                         if volumes.dim() < 5 else "too many values to unpack (expected 5)")
+    B = volumes.shape[0]
+    spec = torch.zeros((B, volumetric.COORD_SPEC), dtype=torch.float32)
+    spec[:, 3:6] = 1.0                                   # step 1 along every axis from the origin
+    spec[:, 9], spec[:, 13], spec[:, 17] = 1.0, 1.0, 1.0   # identity rotation: coordinates are the exact indices
+    with torch.cuda.device(volumes.device):
+        grid = volumetric.coord_volumes_from_specs(spec.to(volumes.device, non_blocking=True), tuple(volumes.shape[2:]))
+    coords, vol = integrate_tensor_3d_with_coordinates(volumes, grid.to(volumes.dtype), softmax=softmax)
+    if not softmax:
+        coords = coords / vol.flatten(2).sum(dim=2, keepdim=True)
+    return coords, vol
 
 
 class _SoftArgmax2D(torch.autograd.Function):

@@ -15,6 +15,7 @@ _TARGETS = (
     ("mvn.utils.op", "unproject_heatmaps", _op.unproject_heatmaps),
     ("mvn.utils.op", "integrate_tensor_3d_with_coordinates", _op.integrate_tensor_3d_with_coordinates),
     ("mvn.utils.op", "integrate_tensor_2d", _op.integrate_tensor_2d),
+    ("mvn.utils.op", "integrate_tensor_3d", _op.integrate_tensor_3d),
     ("mvn.utils.multiview", "triangulate_batch_of_points", _mv.triangulate_batch_of_points),
     ("mvn.utils.multiview", "triangulate_point_from_multiple_views_linear_torch",
      _mv.triangulate_point_from_multiple_views_linear_torch),

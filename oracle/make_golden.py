@@ -79,6 +79,23 @@ def run_softargmax(tag, softmax, **kw):
     npz("softargmax_%s" % tag, softmax=np.array(int(softmax)), **res)
 
 
+def run_softargmax3d_index(tag, softmax, B, J, N, seed):
+    g = torch.Generator().manual_seed(seed)
+    v0 = torch.randn(B, J, *N, generator=g)
+    res = {}
+    for dt, suffix in ((torch.float32, ""), (torch.float64, "64")):
+        v = v0.to(dt).clone().requires_grad_(True)
+        coords, vol = ref_op.integrate_tensor_3d(v, softmax)
+        g2 = torch.Generator().manual_seed(seed + 82)
+        gc = torch.randn(coords.shape, generator=g2)
+        (gv,) = torch.autograd.grad(coords, v, gc.to(dt))
+        if suffix == "":
+            res.update(volumes=v0, coords=coords, prob=vol, grad_coords=gc, grad_volumes=gv)
+        else:
+            res.update(coords64=coords, prob64=vol, grad_volumes64=gv)
+    npz("softargmax3dindex_%s" % tag, softmax=np.array(int(softmax)), **res)
+
+
 def run_softargmax2d(tag, softmax, B, J, H, W, seed, scale=1.0):
     g = torch.Generator().manual_seed(seed)
     hm0 = torch.randn(B, J, H, W, generator=g) * scale
@@ -212,6 +229,8 @@ def main():
     run_softargmax("small_softmax", True, B=2, J=3, N=(5, 6, 7), seed=21, train=True)
     run_softargmax("small_relu", False, B=2, J=3, N=(5, 6, 7), seed=22, train=True)
     run_softargmax("peaked_softmax", True, B=1, J=3, N=12, seed=23, peaked=True, train=True)
+    run_softargmax3d_index("small_softmax", True, B=2, J=3, N=(5, 6, 8), seed=71)
+    run_softargmax3d_index("small_relu", False, B=2, J=3, N=(4, 7, 5), seed=72)
     run_softargmax2d("small_softmax", True, B=2, J=3, H=7, W=9, seed=41)
     run_softargmax2d("small_relu", False, B=2, J=3, H=7, W=9, seed=42)
     run_softargmax2d("sharp_softmax", True, B=1, J=4, H=24, W=24, seed=43, scale=100.0)   # heatmap_multiplier = 100

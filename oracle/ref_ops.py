@@ -232,6 +232,23 @@ class CpuSlabOps:
         return (multiplier * (prob > 0).double() * G).float()
 
 
+def integrate_tensor_3d(volumes, softmax=True):
+    """Voxel-index variant (reference: op.py:50-81): softmax or relu over the flattened volume, marginal masses per axis
+    times arange, relu mode divides by the total mass; returns (coordinates (B,J,3), volumes)."""
+    B, J, nx, ny, nz = volumes.shape
+    flat = volumes.reshape(B, J, -1)
+    flat = F.softmax(flat, dim=2) if softmax else F.relu(flat)
+    vol = flat.reshape(B, J, nx, ny, nz)
+    mass = (vol.sum(dim=3).sum(dim=3), vol.sum(dim=2).sum(dim=3), vol.sum(dim=2).sum(dim=2))
+    out = []
+    for m, n in zip(mass, (nx, ny, nz)):
+        c = (m * torch.arange(n).type(torch.float).to(m.device).to(m.dtype)).sum(dim=2, keepdim=True)
+        if not softmax:
+            c = c / m.sum(dim=2, keepdim=True)
+        out.append(c)
+    return torch.cat(out, dim=2).reshape(B, J, 3), vol
+
+
 # --------------------------------------------------------------------------------------------------------------------
 # 2-D soft-argmax of joint heat maps  (reference: mvn/utils/op.py:11-47)
 # --------------------------------------------------------------------------------------------------------------------

@@ -129,3 +129,31 @@ def test_full_size_properties():
     assert rel_err(prob, p_ref) < 1e-5
     (gv,) = torch.autograd.grad(coords, vol, torch.randn_like(coords))
     assert gv.flatten(2).sum(2).abs().max().item() < 1e-3 * gv.abs().max().item() * 64
+
+
+@pytest.mark.parametrize("name", golden_names("softargmax3dindex_"))
+def test_index_coordinate_variant_golden(name):
+    """integrate_tensor_3d (op.py:50-81): K6 unit grid + K2, against the unmodified reference in fp32 and fp64"""
+    g = load_golden(name)
+    sm = bool(g["softmax"])
+    vol = g["volumes"].cuda().requires_grad_(True)
+    coords, prob = lt_b200.integrate_tensor_3d(vol, sm)
+    assert coords.shape == g["coords"].shape and prob.shape == g["prob"].shape
+    assert (coords.cpu().double() - g["coords64"]).abs().max().item() < 1e-4       # voxel units
+    assert rel_err(prob.cpu(), g["prob64"]) < 1e-5
+    (gv,) = torch.autograd.grad(coords, vol, g["grad_coords"].cuda())
+    assert rel_err(gv.cpu(), g["grad_volumes64"]) < 1e-4
+
+
+def test_index_coordinate_variant_known_answers():
+    vol = torch.full((1, 2, 4, 5, 6), -30.0)
+    vol[0, 0, 3, 1, 4] = 30.0
+    vol[0, 1] = 0.0
+    coords, prob = lt_b200.integrate_tensor_3d(vol.cuda())
+    assert torch.allclose(coords[0, 0].cpu(), torch.tensor([3.0, 1.0, 4.0]), atol=1e-4)
+    assert torch.allclose(coords[0, 1].cpu(), torch.tensor([1.5, 2.0, 2.5]), atol=1e-4)   # uniform -> centre of the grid
+    relu_coords, relu_vol = lt_b200.integrate_tensor_3d(vol.cuda(), softmax=False)
+    assert torch.allclose(relu_coords[0, 0].cpu(), torch.tensor([3.0, 1.0, 4.0]), atol=1e-4)
+    assert torch.isnan(relu_coords[0, 1]).all() and float(relu_vol[0, 1].abs().max()) == 0.0   # 0/0 like the reference
+    with pytest.raises(ValueError):
+        lt_b200.integrate_tensor_3d(vol[0].cuda())

@@ -92,6 +92,7 @@ def test_patch_reference_swaps_the_three_call_sites():
         assert ref_op.integrate_tensor_3d_with_coordinates is lt_b200.op.integrate_tensor_3d_with_coordinates
         assert ref_mv.triangulate_batch_of_points is lt_b200.multiview.triangulate_batch_of_points
         assert ref_op.integrate_tensor_2d is lt_b200.op.integrate_tensor_2d
+        assert ref_op.integrate_tensor_3d is lt_b200.op.integrate_tensor_3d
         import mvn.models.loss as ref_loss
         ref_ce = inspect.signature(lt_b200.VolumetricCELoss.forward)
         assert ref_loss.VolumetricCELoss is lt_b200.loss.VolumetricCELoss

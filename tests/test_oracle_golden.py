@@ -86,6 +86,16 @@ def test_softargmax2d_matches_reference(name):
     assert torch.allclose(c64, g["coords64"], rtol=1e-12, atol=1e-12) and torch.allclose(p64, g["prob64"], rtol=1e-12, atol=1e-15)
 
 
+@pytest.mark.parametrize("name", golden_names("softargmax3dindex_"))
+def test_softargmax3d_index_matches_reference(name):
+    g = load_golden(name)
+    v = g["volumes"].clone().requires_grad_(True)
+    coords, vol = ref_ops.integrate_tensor_3d(v, bool(g["softmax"]))
+    assert torch.allclose(coords, g["coords"], rtol=1e-6, atol=1e-6) and torch.allclose(vol, g["prob"], rtol=1e-6, atol=1e-9)
+    (gv,) = torch.autograd.grad(coords, v, g["grad_coords"])
+    assert rel_err(gv, g["grad_volumes"]) < 1e-6
+
+
 @pytest.mark.parametrize("name", golden_names("coordvol_"))
 def test_coord_volume_matches_reference(name):
     g = load_golden(name)
