@@ -7,22 +7,33 @@
 
 namespace lt {
 
-// softmax over <= 4 views of one channel of one voxel: out = sum_v s_v e^{s_v} / sum_v e^{s_v}.
-// The sum is symmetric in the views, so the maximum is moved to the front with a 3-comparator network and its
-// exponential (exactly 1) is never evaluated: 3 MUFU.EX2 + 1 MUFU.RCP per channel (the SFU is the scarce pipe
-// of this kernel: round 1 ran it at 97 % with expf + IEEE divisions). Absent views carry kNoView (e -> 0).
-// ex2.approx / rcp.approx are good to ~2 ulp, far inside the 1e-5 bar.
-__device__ __forceinline__ float softmax_mix4(float s0, float s1, float s2, float s3) {
-  const float hi1 = fmaxf(s0, s1), lo1 = fminf(s0, s1), hi2 = fmaxf(s2, s3), lo2 = fminf(s2, s3);
-  const float top = fmaxf(hi1, hi2), mid = fminf(hi1, hi2);
-  const float e1 = fast_ex2((lo1 - top) * kLog2eF);
-  const float e2 = fast_ex2((lo2 - top) * kLog2eF);
-  const float e3 = fast_ex2((mid - top) * kLog2eF);
-  const float den = ((1.f + e1) + e2) + e3;
-  float num = fmaf(lo1, e1, top);
-  num = fmaf(lo2, e2, num);
-  num = fmaf(mid, e3, num);
-  return num * fast_rcp(den);
+// softmax over <= 4 views of a channel of one voxel: out = sum_v s_v e^{s_v} / sum_v e^{s_v}, two channels per call.
+// Absent views carry kNoView (e -> 0). ex2.approx / rcp.approx are good to ~2 ulp, far inside the 1e-5 bar (round 1
+// started with expf + IEEE divisions at 97 % SFU load, then a 3-comparator sorting network that skipped the
+// exponential of the maximum; this form trades one more MUFU for half the issue slots).
+// Packed forms (FFMA2 / FMUL2 / FADD2) wherever the ISA has one: shift by the maximum of the four views (3 FMNMX per
+// channel), all four exponentials evaluated (the SFU has room: 30 % busy), numerator and denominator accumulated as
+// pairs. ~15 issue slots per channel instead of ~25.
+__device__ __forceinline__ void softmax_mix4_x2(const float (&a)[4], const float (&b)[4], float& out_a, float& out_b) {
+  const float ma = fmaxf(fmaxf(a[0], a[1]), fmaxf(a[2], a[3]));
+  const float mb = fmaxf(fmaxf(b[0], b[1]), fmaxf(b[2], b[3]));
+  const f2 L2 = pack2(kLog2eF, kLog2eF);
+  const f2 nm = mul2(pack2(-ma, -mb), L2);            // -m*log2e per channel
+  f2 num = pack2(0.f, 0.f), den = pack2(0.f, 0.f);
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    const f2 sv = pack2(a[v], b[v]);
+    float ta, tb;
+    unpack2(fma2(sv, L2, nm), ta, tb);               // (s - m)*log2e, <= 0
+    const f2 e = pack2(fast_ex2(ta), fast_ex2(tb));  // absent views (kNoView) underflow to exactly 0
+    den = add2(den, e);
+    num = fma2(sv, e, num);
+  }
+  float na, nb, da, db;
+  unpack2(num, na, nb);
+  unpack2(den, da, db);
+  out_a = na * fast_rcp(da);
+  out_b = nb * fast_rcp(db);
 }
 
 // AGG: lt_agg.  ALIGNED: N2 % 8 == 0 so every run is a whole, 32-byte aligned sector.
@@ -105,7 +116,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
             }
           }
 #pragma unroll
-          for (int k = 0; k < kCPL; ++k) val[k] = softmax_mix4(s[0][k], s[1][k], s[2][k], s[3][k]);
+          for (int k = 0; k < kCPL; k += 2) {
+            const float ca[4] = {s[0][k], s[1][k], s[2][k], s[3][k]};
+            const float cb[4] = {s[0][k + 1], s[1][k + 1], s[2][k + 1], s[3][k + 1]};
+            softmax_mix4_x2(ca, cb, val[k], val[k + 1]);
+          }
         } else {
           if (v0 == 0) {
 #pragma unroll
