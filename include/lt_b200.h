@@ -9,6 +9,7 @@
  *   lt_softargmax2d_* replaces mvn/utils/op.py:11-47      integrate_tensor_2d
  *   lt_volce_*        replaces mvn/models/loss.py:52-80   VolumetricCELoss.forward
  *   lt_coord_volumes  replaces mvn/models/triangulation.py:306-341  (coordinate-volume construction)
+ *   lt_pwconv_*       replaces mvn/models/triangulation.py:238-240,344-346  (process_features 1x1 convolution)
  *   lt_dlt_*         replaces  mvn/utils/multiview.py:132-174  triangulate_batch_of_points /
  *                                                              triangulate_point_from_multiple_views_linear_torch
  *
@@ -157,6 +158,24 @@ int lt_volce_bwd_sparse(const float *prob, const int *idx, const float *validity
 int lt_softargmax_bwd_add_sparse(const float *prob, const int *idx, const float *vals, float *grad_vol,
                                  int B, int J, long long nvox, int softmax, float multiplier,
                                  void *stream);
+
+/* ---- K7: process_features, the 1x1 convolution in front of K1  (mvn/models/triangulation.py:238-240, 344-346) ----
+ * The reference applies nn.Conv2d(256, 32, 1) to the backbone's features (B*V, Cin, H, W) and hands the result
+ * to unproject_heatmaps. lt_pwconv_fwd computes out[n,c,y,x] = bias[c] + sum_k weight[c,k] * x[n,k,y,x] and writes it
+ * DIRECTLY in the gather layout of K0 (out_hwcp: lt_feat_layout_elems(BV, Cout, H, W) floats, zero border and zero
+ * padded channels included), so lt_feat_to_hwc is not needed between the two.  weight (Cout, Cin) row-major = the
+ * (Cout, Cin, 1, 1) tensor of nn.Conv2d; bias (Cout) or NULL.  fp32 FMA chain over k ascending (deterministic).
+ * Backward: grad_hwcp is the gradient map lt_unproject_bwd scatters into (same layout; border and padded channels are
+ * ignored).  grad_x (BV, Cin, H, W) fully overwritten; grad_weight (Cout, Cin) and grad_bias (Cout, may be NULL) fully
+ * overwritten, summed in a fixed order (deterministic).  ws: lt_pwconv_ws_bytes() bytes of scratch, 16-byte aligned
+ * (forward and backward-weight; may be shared, contents are not kept between calls). */
+size_t lt_pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W);
+int lt_pwconv_fwd(const float *x, const float *weight, const float *bias, float *out_hwcp, void *ws,
+                  int BV, int Cin, int Cout, int H, int W, void *stream);
+int lt_pwconv_bwd_data(const float *grad_hwcp, const float *weight, float *grad_x, int BV, int Cin,
+                       int Cout, int H, int W, void *stream);
+int lt_pwconv_bwd_weight(const float *x, const float *grad_hwcp, float *grad_weight, float *grad_bias,
+                         void *ws, int BV, int Cin, int Cout, int H, int W, void *stream);
 
 /* ---- K3: batched confidence-weighted DLT  (multiview.py:132-174) -------------------------------
  * proj (B,V,3,4)  pts (B,V,J,2)  conf (B,V,J) or NULL (=> ones, multiview.py:147-148)

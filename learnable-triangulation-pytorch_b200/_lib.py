@@ -46,6 +46,10 @@ SIGNATURES = {
     "lt_volce_bwd": (_i, [_vp] * 5 + [_i, _i, _ll, _vp]),
     "lt_volce_bwd_sparse": (_i, [_vp] * 6 + [_i, _i, _ll, _vp]),
     "lt_softargmax_bwd_add_sparse": (_i, [_vp] * 4 + [_i, _i, _ll, _i, _f, _vp]),
+    "lt_pwconv_ws_bytes": (ctypes.c_size_t, [_i] * 5),
+    "lt_pwconv_fwd": (_i, [_vp] * 5 + [_i] * 5 + [_vp]),
+    "lt_pwconv_bwd_data": (_i, [_vp] * 3 + [_i] * 5 + [_vp]),
+    "lt_pwconv_bwd_weight": (_i, [_vp] * 5 + [_i] * 5 + [_vp]),
     "lt_dlt_fwd": (_i, [_vp] * 5 + [_i, _i, _i, _vp]),
     "lt_dlt_bwd": (_i, [_vp] * 7 + [_i, _i, _i, _vp]),
 }

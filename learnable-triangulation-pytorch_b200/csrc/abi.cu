@@ -224,6 +224,49 @@ LT_API int lt_softargmax_bwd_add_sparse(const float* prob, const int* idx, const
                                                                multiplier, as_stream(stream)));
 }
 
+LT_API size_t lt_pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W) {
+  if (BV <= 0 || Cin <= 0 || Cout <= 0 || H <= 0 || W <= 0) return 0;
+  return lt::pwconv_ws_bytes(BV, Cin, Cout, H, W);
+}
+
+static bool bad_pwconv_shape(int BV, int Cin, int Cout, int H, int W) {
+  return BV < 0 || Cin < 1 || Cout < 1 || H < 1 || W < 1 || BV > 65535 || (long long)H * W > 0x3fffffffLL ||
+         (long long)BV * ((long long)H * W / 16 + 1) > 0x7fffffffLL;
+}
+
+LT_API int lt_pwconv_fwd(const float* x, const float* weight, const float* bias, float* out_hwcp, void* ws, int BV,
+                         int Cin, int Cout, int H, int W, void* stream) {
+  LT_REQUIRE(!bad_pwconv_shape(BV, Cin, Cout, H, W), "bad shape");
+  if (BV == 0) return 0;
+  LT_REQUIRE(x && weight && out_hwcp && ws, "null pointer");
+  LT_REQUIRE(((uintptr_t)ws & 15) == 0 && ((uintptr_t)out_hwcp & 15) == 0, "ws / out_hwcp must be 16-byte aligned");
+  return finish(__func__, lt::launch_pwconv_fwd(x, weight, bias, out_hwcp, ws, BV, Cin, Cout, H, W, as_stream(stream)));
+}
+
+LT_API int lt_pwconv_bwd_data(const float* grad_hwcp, const float* weight, float* grad_x, int BV, int Cin, int Cout,
+                              int H, int W, void* stream) {
+  LT_REQUIRE(!bad_pwconv_shape(BV, Cin, Cout, H, W), "bad shape");
+  if (BV == 0) return 0;
+  LT_REQUIRE(grad_hwcp && weight && grad_x, "null pointer");
+  LT_REQUIRE(((uintptr_t)grad_hwcp & 15) == 0, "grad_hwcp must be 16-byte aligned");
+  return finish(__func__, lt::launch_pwconv_bwd_data(grad_hwcp, weight, grad_x, BV, Cin, Cout, H, W, as_stream(stream)));
+}
+
+LT_API int lt_pwconv_bwd_weight(const float* x, const float* grad_hwcp, float* grad_weight, float* grad_bias, void* ws,
+                                int BV, int Cin, int Cout, int H, int W, void* stream) {
+  LT_REQUIRE(!bad_pwconv_shape(BV, Cin, Cout, H, W), "bad shape");
+  LT_REQUIRE(grad_weight, "null pointer");
+  if (BV == 0) {  // an empty batch has a zero gradient
+    cudaError_t e = cudaMemsetAsync(grad_weight, 0, (size_t)Cin * Cout * 4, as_stream(stream));
+    if (e == cudaSuccess && grad_bias) e = cudaMemsetAsync(grad_bias, 0, (size_t)Cout * 4, as_stream(stream));
+    return finish(__func__, e);
+  }
+  LT_REQUIRE(x && grad_hwcp && ws, "null pointer");
+  LT_REQUIRE(((uintptr_t)ws & 15) == 0 && ((uintptr_t)grad_hwcp & 15) == 0, "ws / grad_hwcp must be 16-byte aligned");
+  return finish(__func__, lt::launch_pwconv_bwd_weight(x, grad_hwcp, grad_weight, grad_bias, ws, BV, Cin, Cout, H, W,
+                                                       as_stream(stream)));
+}
+
 LT_API int lt_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out, double* saved, int B, int V,
                int J, void* stream) {
   LT_REQUIRE(B >= 0 && J >= 0, "negative extent");

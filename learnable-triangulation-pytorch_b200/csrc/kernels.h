@@ -54,6 +54,14 @@ cudaError_t launch_softargmax2d_bwd(const float* prob, const float* coords, cons
                                     const float* grad_prob, float* grad_hm, int BJ, int H, int W, int softmax,
                                     float mult, cudaStream_t st);
 
+size_t pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W);
+cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* bias, float* out_hwcp, void* ws, int BV,
+                              int Cin, int Cout, int H, int W, cudaStream_t st);
+cudaError_t launch_pwconv_bwd_data(const float* grad_hwcp, const float* weight, float* grad_x, int BV, int Cin,
+                                   int Cout, int H, int W, cudaStream_t st);
+cudaError_t launch_pwconv_bwd_weight(const float* x, const float* grad_hwcp, float* grad_weight, float* grad_bias,
+                                     void* ws, int BV, int Cin, int Cout, int H, int W, cudaStream_t st);
+
 cudaError_t launch_dlt_fwd(const float* proj, const float* pts, const float* conf, float* out,
                            double* saved, int B, int V, int J, cudaStream_t st);
 cudaError_t launch_dlt_bwd(const float* grad_out, const float* proj, const float* pts, const float* conf,

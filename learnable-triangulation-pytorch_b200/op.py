@@ -43,6 +43,57 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+# ---- tensors that already live in the gather layout -----------------------------------------------------------------
+# triangulation.process_features writes K1's gather layout "hwcp" directly and returns a strided (B*V,C,H,W) view of its
+# interior; K1's backward hands its gradient map back the same way. Such buffers are remembered by the address and size of
+# their storage; a tensor is taken as "already hwcp" only if its storage is one of them AND its strides/offset are exactly
+# the interior view (also after the `.view(batch_size, n_views, ...)` of triangulation.py:346). Anything else takes K0.
+_HWCP = {}  # storage address -> (kind, number of floats); kind 'feat' has a zero border, 'grad' has a scratch border
+
+
+def _hwcp_register(base, kind):
+    if len(_HWCP) > 4096:
+        _HWCP.clear()
+    _HWCP[base.untyped_storage().data_ptr()] = (kind, base.numel())
+
+
+def _hwcp_view(base, lead, C, H, W):
+    """Interior of the 1-D gather-layout buffer `base` as a strided (*lead, C, H, W) tensor (no copy)."""
+    Cp = _lib.lib().lt_padded_channels(C)
+    Wp, S = W + 2, (H + 2) * (W + 2) * Cp
+    strides, acc = [], S
+    for n in reversed(lead):
+        strides.insert(0, acc)
+        acc *= n
+    return base.as_strided(tuple(lead) + (C, H, W), tuple(strides) + (1, Wp * Cp, Cp), (Wp + 1) * Cp)
+
+
+def _hwcp_base(t, kind):
+    """The 1-D gather-layout buffer behind `t` (*lead, C, H, W) if `t` is exactly its interior view, else None."""
+    if t.dtype != torch.float32 or not t.is_cuda or t.dim() < 4 or t.numel() == 0:
+        return None
+    st = t.untyped_storage()
+    entry = _HWCP.get(st.data_ptr())
+    if entry is None or entry[0] != kind:
+        return None
+    *lead, C, H, W = t.shape
+    Cp = _lib.lib().lt_padded_channels(C)
+    Wp, S = W + 2, (H + 2) * (W + 2) * Cp
+    n = 1
+    for d in lead:
+        n *= d
+    if entry[1] != n * S or st.nbytes() != n * S * 4 or t.storage_offset() != (Wp + 1) * Cp:
+        return None
+    want, acc = [], S
+    for d in reversed(lead):
+        want.insert(0, acc)
+        acc *= d
+    want += [1, Wp * Cp, Cp]
+    if any(sz != 1 and a != b for sz, a, b in zip(t.shape, t.stride(), want)):
+        return None
+    return torch.empty(0, device=t.device, dtype=torch.float32).set_(st, 0, (n * S,), (1,))
+
+
 class _Unproject(torch.autograd.Function):
     @staticmethod
     def forward(ctx, heatmaps, proj, coord, conf, agg, align_corners):
@@ -51,18 +102,21 @@ class _Unproject(torch.autograd.Function):
         N0, N1, N2 = coord.shape[1:4]
         with torch.cuda.device(heatmaps.device):
             st = _stream()
-            hm = _f32c(heatmaps)
             proj_c, coord_c = _f32c(proj), _f32c(coord)
             conf_c = _f32c(conf) if conf is not None else None
-            # K0: gather layout (channels-last, padded channels, zero border) of the feature maps; opaque to this side
-            feat = torch.empty((L.lt_feat_layout_elems(B * V, C, H, W),), device=hm.device, dtype=torch.float32)
-            _lib.check(L.lt_feat_to_hwc(_lib.ptr(hm), _lib.ptr(feat), B * V, C, H, W, st))
-            out = torch.empty((B, C, N0, N1, N2), device=hm.device, dtype=torch.float32)
+            feat = _hwcp_base(heatmaps, 'feat')  # written in the gather layout by K7 (process_features): no K0
+            from_hwcp = feat is not None
+            if not from_hwcp:
+                hm = _f32c(heatmaps)
+                # K0: gather layout (channels-last, padded channels, zero border) of the feature maps; opaque to this side
+                feat = torch.empty((L.lt_feat_layout_elems(B * V, C, H, W),), device=hm.device, dtype=torch.float32)
+                _lib.check(L.lt_feat_to_hwc(_lib.ptr(hm), _lib.ptr(feat), B * V, C, H, W, st))
+            out = torch.empty((B, C, N0, N1, N2), device=feat.device, dtype=torch.float32)
             _lib.check(L.lt_unproject_fwd(_lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c), _lib.ptr(conf_c),
                                           _lib.ptr(out), B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
         ctx.save_for_backward(feat, proj_c, coord_c, conf_c)
         ctx.meta = (B, V, C, H, W, N0, N1, N2, agg, align_corners, heatmaps.dtype,
-                    conf.dtype if conf is not None else None)
+                    conf.dtype if conf is not None else None, from_hwcp)
         return out
 
     @staticmethod
@@ -70,7 +124,7 @@ class _Unproject(torch.autograd.Function):
     def backward(ctx, grad_out):
         L = _lib.lib()
         feat, proj_c, coord_c, conf_c = ctx.saved_tensors
-        B, V, C, H, W, N0, N1, N2, agg, align_corners, hm_dtype, conf_dtype = ctx.meta
+        B, V, C, H, W, N0, N1, N2, agg, align_corners, hm_dtype, conf_dtype, from_hwcp = ctx.meta
         need_hm, need_conf = ctx.needs_input_grad[0], ctx.needs_input_grad[3] and conf_c is not None
         g_hm = g_conf = None
         if not (need_hm or need_conf):
@@ -87,7 +141,11 @@ class _Unproject(torch.autograd.Function):
             _lib.check(L.lt_unproject_bwd(_lib.ptr(go), _lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c),
                                           _lib.ptr(conf_c), _lib.ptr(gfeat), _lib.ptr(gconf), _lib.ptr(ws),
                                           B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
-            if need_hm:
+            if need_hm and from_hwcp:
+                # the producer (K7's backward) reads the gradient map in place: hand its interior back as a view
+                _hwcp_register(gfeat, 'grad')
+                g_hm = _hwcp_view(gfeat, (B, V), C, H, W)
+            elif need_hm:
                 g_hm = torch.empty((B, V, C, H, W), device=feat.device, dtype=torch.float32)
                 _lib.check(L.lt_feat_to_chw(_lib.ptr(gfeat), _lib.ptr(g_hm), B * V, C, H, W, st))
                 g_hm = g_hm.to(hm_dtype)

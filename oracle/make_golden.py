@@ -210,8 +210,37 @@ def run_dlt(tag, **kw):
         grad_confidences64=(conf64.grad if conf64 is not None else None))
 
 
+def run_process_features(tag, BV, H, W, seed, views=None):
+    """`process_features` of an actual reference VolumetricTriangulationNet (triangulation.py:238-240), applied the way
+    forward() applies it (:344-346), with the gradients autograd gives for a seeded upstream gradient."""
+    from types import SimpleNamespace as NS
+    from mvn.models.triangulation import VolumetricTriangulationNet
+    cfg = NS(model=NS(backbone=NS(num_joints=17, num_layers=18, style="simple", init_weights=False, checkpoint=None,
+                                  alg_confidences=False, vol_confidences=False),
+                      volume_aggregation_method="softmax", volume_softmax=True, volume_multiplier=1.0, volume_size=64,
+                      cuboid_side=2500.0, kind="mpii", use_gt_pelvis=False, heatmap_softmax=True,
+                      heatmap_multiplier=100.0))
+    torch.manual_seed(seed)
+    net = VolumetricTriangulationNet(cfg, device="cpu")
+    conv = net.process_features[0]
+    gen = torch.Generator().manual_seed(seed + 1)
+    views = views or 1
+    feats = torch.randn(BV // views, views, conv.in_channels, H, W, generator=gen).requires_grad_(True)
+    x = feats.view(-1, *feats.shape[2:])                               # triangulation.py:344
+    y = net.process_features(x)                                        # :345
+    y5 = y.view(BV // views, views, *y.shape[1:])                      # :346
+    gy = torch.randn(y5.shape, generator=gen)
+    y5.backward(gy)
+    npz("pwconv_" + tag, features=feats.detach(), weight=conv.weight.detach(), bias=conv.bias.detach(), out=y5.detach(),
+        grad_out=gy, grad_features=feats.grad, grad_weight=conv.weight.grad, grad_bias=conv.bias.grad)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if os.environ.get("LT_GOLDEN_ONLY") == "pwconv":
+        run_process_features("small", BV=4, H=6, W=10, seed=81, views=2)
+        run_process_features("ragged", BV=3, H=5, W=7, seed=82, views=3)      # H*W % 4 != 0: the 4-byte copy path
+        return
     torch.set_num_threads(4)
     small = dict(B=2, V=3, C=6, H=10, W=12, N=(5, 6, 7), seed=11, train=True, inside_view=True, side=2500.0)
     for method in ("sum", "conf", "conf_norm", "max", "softmax"):
@@ -243,6 +272,8 @@ def main():
     run_dlt("noconf", B=2, V=3, J=4, seed=32, with_conf=False)
     run_dlt("manyview", B=1, V=31, J=6, seed=33, dome=True)
     run_dlt("twoview", B=2, V=2, J=3, seed=34)
+    run_process_features("small", BV=4, H=6, W=10, seed=81, views=2)
+    run_process_features("ragged", BV=3, H=5, W=7, seed=82, views=3)      # H*W % 4 != 0: the 4-byte copy path
 
 
 if __name__ == "__main__":

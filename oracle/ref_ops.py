@@ -272,6 +272,14 @@ def integrate_tensor_2d(heatmaps, softmax=True):
 # --------------------------------------------------------------------------------------------------------------------
 # coordinate volumes  (reference: mvn/models/triangulation.py:306-341 + mvn/utils/volumetric.py:87-114)
 # --------------------------------------------------------------------------------------------------------------------
+def process_features(features, weight, bias=None):
+    """The `process_features` step of VolumetricTriangulationNet: `nn.Sequential(nn.Conv2d(256, 32, 1))`
+    (mvn/models/triangulation.py:238-240) applied to the (B*V, 256, H, W) backbone features (:344-346)."""
+    if weight.dim() == 2:
+        weight = weight[:, :, None, None]
+    return F.conv2d(features, weight, bias)
+
+
 def build_coord_volume(base_point, cuboid_side, volume_size, theta, axis, transfer_cmu_to_human36m=False,
                        device="cpu"):
     """One item, the same torch statements as the reference block: meshgrid -> position + step * index per axis

@@ -146,3 +146,20 @@ def test_dlt_noise_free_recovers_points():
     out = ref_ops.triangulate_batch_of_points(d["proj_matricies"].double(), d["points"].double(),
                                               d["confidences"].double(), out_dtype=None)
     assert (out - d["points_3d"].double()).abs().max().item() < 0.05  # fp32 rounding of the 2-D points only
+
+
+@pytest.mark.parametrize("name", golden_names("pwconv_"))
+def test_process_features_matches_reference(name):
+    """oracle.process_features == the `process_features` module of a real reference VolumetricTriangulationNet
+    (triangulation.py:238-240) applied as in forward() (:344-346), values and all three gradients."""
+    g = load_golden(name)
+    f5 = g["features"].clone().requires_grad_(True)
+    w = g["weight"].clone().requires_grad_(True)
+    b = g["bias"].clone().requires_grad_(True)
+    y = ref_ops.process_features(f5.view(-1, *f5.shape[2:]), w, b)
+    y5 = y.view(f5.shape[0], f5.shape[1], *y.shape[1:])
+    assert y5.shape == g["out"].shape and rel_err(y5, g["out"]) < 1e-6
+    y5.backward(g["grad_out"])
+    assert rel_err(f5.grad, g["grad_features"]) < 1e-6
+    assert rel_err(w.grad, g["grad_weight"]) < 1e-5
+    assert rel_err(b.grad, g["grad_bias"]) < 1e-5
