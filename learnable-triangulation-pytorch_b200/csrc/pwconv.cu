@@ -13,6 +13,8 @@
 // K = 256) but stays on the FMA pipe as packed FFMA2: the parity bar is the fp32 oracle, and single-pass TF32 tensor-core
 // products are 1e-3 away from it (a 3xTF32 tcgen05 version is the listed follow-up). Bounds: forward and
 // backward-data read or write the (B·V,256,H,W) tensor once (HBM floor) and issue 2·Cin·Cout flops per pixel (FFMA2 floor).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -365,11 +367,254 @@ __global__ void __launch_bounds__(256) k_pw_reduce_partials(const float* __restr
   }
 }
 
+
+// ---- forward on the 5th-generation tensor cores: tcgen05.mma kind::tf32 with a three-product split --------------------
+// TF32 keeps 10 mantissa bits, the parity bar is fp32. Every operand is split x = hi + lo (hi = the top 19 bits of x,
+// lo = x - hi, exact in fp32) and D += hi·hi + lo·hi + hi·lo: the dropped lo·lo term is 2^-22 relative, the accumulator
+// lives in TMEM as fp32. Per CTA (one per SM, persistent over 128-pixel tiles):
+//   warps 0-15  producers: coalesced LDG of X (pixel-contiguous), split, STS.128 of hi and lo tiles in the UMMA
+//               canonical K-major no-swizzle layout (core matrix = 8 pixels x 16 bytes), four stages prefetched in registers
+//   warp  16    one elected lane issues 3 x tcgen05.mma (M=128 pixels, N=32 channels, K=8) per 8 input channels and
+//               commits each stage back to the producers through an mbarrier
+//   warps 17-20 epilogue: tcgen05.ld of the 128 x 32 accumulator (one pixel per thread), + bias, four 32-byte stores =
+//               the 128-byte texel of the gather layout; TMEM is double buffered so tile t drains under tile t+1.
+// W (32 x Cin) is split once per CTA into two resident K-major tiles.
+namespace tc {
+constexpr int kM = 128, kN = 32, kKs = 32, kStagesTc = 3;
+constexpr int kGroups = kStagesTc, kProducerWarps = 4 * kGroups, kMmaWarp = kProducerWarps, kWarps = kProducerWarps + 5;
+// warps 0-11: three producer groups of 128 threads (group g fills ring slot g); warp 12: MMA; warps 13-16: epilogue (warp & 3 = 1,2,3,0)
+constexpr uint32_t kTileBytes = kM * kKs * 4;            // 16 KB: one hi or lo tile of a stage
+constexpr uint32_t kStageBytes = 2 * kTileBytes;
+constexpr uint32_t kLboA = (kM / 8) * 128, kSboA = 128;  // A tile: [k4][pixel group of 8][8 pixels][16 B]
+constexpr uint32_t kLboB = 128;                          // W tile: [channel group of 8][k4][8 channels][16 B]
+constexpr uint32_t idesc_tf32(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kM >> 4) << 24); }
+constexpr uint32_t kSpinLimit = 1u << 27;
+// Back-to-back tcgen05.mma into ONE accumulator serialise on the accumulate latency (measured: ~143 cycles per 16-cycle
+// M128 N32 K8 instruction). Independent accumulators per tile (3 products x even/odd k8 step) keep several in flight; the
+// epilogue adds them. Two tile buffers of 6 x 32 columns = 384 of the 512 TMEM columns.
+constexpr uint32_t kAccPerTile = 6, kBufCols = kAccPerTile * kN, kTmemCols = 512;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+// bounded spin: a protocol error traps (the launch fails loudly) instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+  const uint32_t a = smem_u32(b);
+  for (uint32_t i = 0; i < kSpinLimit; ++i) {
+    uint32_t done;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    if (done) return;
+  }
+  __trap();
+}
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* b) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void proxy_fence() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+  hi = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+  lo = x - hi;
+}
+
+__global__ void __launch_bounds__(kWarps * 32, 1)
+    k_pwconv_fwd_tc(const float* __restrict__ X, const float* __restrict__ Wm, const float* __restrict__ bias,
+                    float* __restrict__ out, int Cin, int Cout, int Cp, int H, int W, int tiles_per_img, int ntiles) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  unsigned char* sA = sm;
+  unsigned char* sW = sm + kStagesTc * kStageBytes;
+  const uint32_t wbytes = (uint32_t)kN * Cin * 4;                 // one of the two W tiles
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sW + 2 * wbytes);
+  uint64_t *full = bars, *empty = bars + kStagesTc, *tfull = bars + 2 * kStagesTc, *tempty = bars + 2 * kStagesTc + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStagesTc + 4);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int HW = H * W, nks = Cin / kKs;
+  const uint32_t sboB = (uint32_t)(Cin / 4) * 128;
+
+  if (tid == 0) {
+    for (int s = 0; s < kStagesTc; ++s) { mbar_init(full + s, 4); mbar_init(empty + s, 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kMmaWarp) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (int idx = tid; idx < kN * Cin; idx += kWarps * 32) {
+    const int n = idx / Cin, k = idx - n * Cin;
+    float hi, lo;
+    split_tf32(n < Cout ? __ldg(Wm + (size_t)n * Cin + k) : 0.f, hi, lo);
+    const uint32_t off = (uint32_t)(n >> 3) * sboB + (uint32_t)(k >> 2) * kLboB + (n & 7) * 16 + (k & 3) * 4;
+    *reinterpret_cast<float*>(sW + off) = hi;
+    *reinterpret_cast<float*>(sW + wbytes + off) = lo;
+  }
+  proxy_fence();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int my_tiles = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (warp < kProducerWarps) {
+    // Producer group g = warp / 4 owns ring slot g and every kGroups-th stage: a warp's chain (wait for the slot, split,
+    // store, proxy fence, arrive) then has kGroups stage times to finish instead of one. A thread owns one pixel and all
+    // 32 input channels of its stage, and keeps the loads of its NEXT stage in flight in registers
+    // (384 threads x up to 64 loads x 4 B = 96 KB per SM; HBM latency x bandwidth needs ~35 KB).
+    const int grp = warp >> 2, px = tid & (kM - 1);
+    const int total = my_tiles * nks;
+    int l_j = grp;                                  // stage index of the load stream (tile-major, then channel block)
+    auto load = [&](float (&v)[kKs]) {
+      if (l_j >= total) return;
+      const int t = l_j / nks, ks = l_j - t * nks;
+      const int tile = blockIdx.x + t * gridDim.x;
+      const int bv = tile / tiles_per_img, p = (tile - bv * tiles_per_img) * kM + px;
+      if (p < HW) {
+        const float* src = X + ((size_t)bv * Cin + ks * kKs) * HW + p;
+#pragma unroll
+        for (int i = 0; i < kKs; ++i) v[i] = __ldg(src + (size_t)i * HW);
+      } else {
+#pragma unroll
+        for (int i = 0; i < kKs; ++i) v[i] = 0.f;
+      }
+      l_j += kGroups;
+    };
+    uint32_t s_par = 1;                             // parity of this slot's `empty` barrier
+    unsigned char* const base = sA + grp * kStageBytes + (px >> 3) * kSboA + (px & 7) * 16;
+    auto store = [&](const float (&v)[kKs]) {
+      mbar_wait(empty + grp, s_par);
+      s_par ^= 1;
+#pragma unroll
+      for (int q = 0; q < kKs / 4; ++q) {
+        float4 hi, lo;
+        split_tf32(v[4 * q + 0], hi.x, lo.x);
+        split_tf32(v[4 * q + 1], hi.y, lo.y);
+        split_tf32(v[4 * q + 2], hi.z, lo.z);
+        split_tf32(v[4 * q + 3], hi.w, lo.w);
+        *reinterpret_cast<float4*>(base + q * kLboA) = hi;
+        *reinterpret_cast<float4*>(base + kTileBytes + q * kLboA) = lo;
+      }
+      proxy_fence();   // generic-proxy writes -> visible to the tensor core's async-proxy reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full + grp);
+    };
+    float b0[kKs], b1[kKs];
+    load(b0);
+    for (int j = grp; j < total; j += 2 * kGroups) {
+      load(b1); store(b0);
+      if (j + kGroups < total) { load(b0); store(b1); }
+    }
+  } else if (warp == kMmaWarp) {
+    if (lane == 0) {
+      int j = 0;
+      for (int t = 0; t < my_tiles; ++t) {
+        const int buf = t & 1;
+        mbar_wait(tempty + buf, ((t >> 1) & 1) ^ 1);   // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d = tmem_base + buf * kBufCols;
+        for (int ks = 0; ks < nks; ++ks, ++j) {
+          const int slot = j % kStagesTc;
+          mbar_wait(full + slot, (j / kStagesTc) & 1);
+          tc_fence_after();
+          const uint32_t a_hi = smem_u32(sA + slot * kStageBytes), a_lo = a_hi + kTileBytes;
+#pragma unroll
+          for (int k8 = 0; k8 < kKs / 8; ++k8) {
+            const uint32_t aoff = (uint32_t)k8 * 2 * kLboA, boff = (uint32_t)((ks * kKs + k8 * 8) >> 2) * kLboB;
+            const uint64_t ah = umma_desc(a_hi + aoff, kLboA, kSboA), al = umma_desc(a_lo + aoff, kLboA, kSboA);
+            // W_lo sits right behind W_hi with the same channel-group stride: one N = 64 instruction multiplies A_hi by
+            // both (columns 0-31 hi·hi, 32-63 hi·lo), so A_hi is fetched from shared memory once instead of twice
+            const uint64_t bh = umma_desc(smem_u32(sW) + boff, kLboB, sboB);
+            const uint32_t acc = (ks != 0 || k8 >= 2) ? 1u : 0u, dk = d + (k8 & 1) * 3 * kN;
+            umma_tf32(dk, ah, bh, idesc_tf32(2 * kN), acc);
+            umma_tf32(dk + 2 * kN, al, bh, idesc_tf32(kN), acc);
+          }
+          umma_commit(empty + slot);     // stage reusable once these MMAs have read it
+        }
+        umma_commit(tfull + buf);        // accumulator complete
+      }
+    }
+  } else {
+    const int q = warp & 3;              // TMEM lane quarter this warp may read
+    const int Hp = H + 2, Wp = W + 2;
+    float* s_bias = reinterpret_cast<float*>(tmem_slot + 1);   // 32 floats behind the barriers (zero padded)
+    if (warp == kMmaWarp + 1) s_bias[lane] = (bias != nullptr && lane < Cout) ? __ldg(bias + lane) : 0.f;
+    asm volatile("bar.sync 1, 128;" ::: "memory");             // the four epilogue warps only
+    for (int t = 0; t < my_tiles; ++t) {
+      const int buf = t & 1;
+      const int tile = blockIdx.x + t * gridDim.x;
+      mbar_wait(tfull + buf, (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * kBufCols + ((uint32_t)(q * 32) << 16);
+      float acc[kN];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {          // 16 columns at a time: small terms (lo products) first, hi·hi last
+#pragma unroll
+        for (int a = 0; a < (int)kAccPerTile; ++a) {
+          const int which = (a < 4) ? 1 + (a >> 1) + (a & 1) * 3 : (a & 1) * 3;   // blocks 1,4,2,5 (hi·lo, lo·hi), then 0,3 (hi·hi)
+          uint32_t r[16];
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+              : "r"(taddr + which * kN + h * 16) : "memory");
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int i = 0; i < 16; ++i) acc[h * 16 + i] = (a == 0) ? __uint_as_float(r[i]) : acc[h * 16 + i] + __uint_as_float(r[i]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty + buf);
+      const int bv = tile / tiles_per_img, p = (tile - bv * tiles_per_img) * kM + q * 32 + lane;
+      if (p < HW) {
+        const int y = p / W, x = p - y * W;
+        float* dst = out + (((size_t)bv * Hp + y + 1) * Wp + x + 1) * Cp;
+#pragma unroll
+        for (int c8 = 0; c8 < kN / 8; ++c8) {
+          float v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = acc[c8 * 8 + i] + s_bias[c8 * 8 + i];
+          stg256(dst + c8 * 8, v);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+  }
+}
+
+inline size_t smem_bytes(int Cin) { return (size_t)kStagesTc * kStageBytes + 2 * (size_t)kN * Cin * 4 + 256; }
+inline bool usable(int Cin, int Cout) { return Cout <= kN && Cin % kKs == 0 && Cin >= kKs && Cin <= 256; }
+}  // namespace tc
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 constexpr int kFwdSmem = kStages * (kKc * kPx + kKc * kCo) * 4;      // 73,728 B -> 3 CTAs per SM
 constexpr int kBwdDataSmem = (kCo * kPx + kCo * kKn) * 4;            // 65,536 B -> 3 CTAs per SM
 constexpr int kBwdWeightSmem = kWgStages * kWgStageFloats * 4;       // 90,112 B -> 2 CTAs per SM
 constexpr int kWeightWorkers = 2 * 148;                              // persistent: 2 CTAs on each of the 148 SMs
+
+// developer knob for A/B measurements (tools/bench_process_features.py): LT_B200_PWCONV=ffma keeps the forward on the
+// FMA pipe. Read once; both paths compute the same fp32 result to 1e-6.
+bool force_ffma() {
+  static const bool v = [] { const char* e = getenv("LT_B200_PWCONV"); return e != nullptr && e[0] == 'f'; }();
+  return v;
+}
 
 int weight_workers(int BV, int H, int W) {
   const long long total = (long long)BV * ((H * W + kWgPx - 1) / kWgPx);
@@ -389,6 +634,16 @@ size_t pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W) {
 cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* bias, float* out_hwcp, void* ws,
                               int BV, int Cin, int Cout, int H, int W, cudaStream_t st) {
   const int Cp = padded_channels(Cout), HW = H * W;
+  if (tc::usable(Cin, Cout) && !force_ffma()) {
+    k_pw_zero_border<<<BV, 256, 0, st>>>(out_hwcp, Cp, H, W);
+    const int tiles_per_img = (HW + tc::kM - 1) / tc::kM, ntiles = BV * tiles_per_img;
+    const int smem = (int)tc::smem_bytes(Cin);
+    cudaError_t e = cudaFuncSetAttribute(tc::k_pwconv_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    tc::k_pwconv_fwd_tc<<<ntiles < 148 ? ntiles : 148, tc::kWarps * 32, smem, st>>>(x, weight, bias, out_hwcp, Cin, Cout,
+                                                                                  Cp, H, W, tiles_per_img, ntiles);
+    return cudaGetLastError();
+  }
   float* Wt = static_cast<float*>(ws);
   k_pw_transpose_weight<<<(Cin * Cp + 255) / 256, 256, 0, st>>>(weight, Wt, Cin, Cout, Cp);
   k_pw_zero_border<<<BV, 256, 0, st>>>(out_hwcp, Cp, H, W);
