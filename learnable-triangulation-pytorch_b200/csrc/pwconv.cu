@@ -370,29 +370,31 @@ __global__ void __launch_bounds__(256) k_pw_reduce_partials(const float* __restr
 
 // ---- forward on the 5th-generation tensor cores: tcgen05.mma kind::tf32 with a three-product split --------------------
 // TF32 keeps 10 mantissa bits, the parity bar is fp32. Every operand is split x = hi + lo (hi = the top 19 bits of x,
-// lo = x - hi, exact in fp32) and D += hi·hi + lo·hi + hi·lo: the dropped lo·lo term is 2^-22 relative, the accumulator
-// lives in TMEM as fp32. Per CTA (one per SM, persistent over 128-pixel tiles):
-//   warps 0-15  producers: coalesced LDG of X (pixel-contiguous), split, STS.128 of hi and lo tiles in the UMMA
-//               canonical K-major no-swizzle layout (core matrix = 8 pixels x 16 bytes), four stages prefetched in registers
-//   warp  16    one elected lane issues 3 x tcgen05.mma (M=128 pixels, N=32 channels, K=8) per 8 input channels and
-//               commits each stage back to the producers through an mbarrier
-//   warps 17-20 epilogue: tcgen05.ld of the 128 x 32 accumulator (one pixel per thread), + bias, four 32-byte stores =
-//               the 128-byte texel of the gather layout; TMEM is double buffered so tile t drains under tile t+1.
-// W (32 x Cin) is split once per CTA into two resident K-major tiles.
+// lo = x - hi, exact in fp32) and D += hi·hi + hi·lo + lo·hi: the dropped lo·lo term is 2^-22 relative, the accumulators
+// live in TMEM as fp32. Per CTA (one per SM, persistent over 128-pixel tiles):
+//   warps 0-11  three producer groups of 128 threads, group g takes every third 32-channel stage: coalesced LDG of X
+//               (a thread = one pixel), split, and tcgen05.st of the hi and lo rows STRAIGHT INTO TENSOR MEMORY — the A
+//               operand never touches shared memory (an earlier version staged it there as UMMA canonical tiles: the STS
+//               of hi+lo plus the tensor core's operand fetches kept the L1/shared data pipe 72 % busy and capped the
+//               kernel at 170 us; measured, profiles/). The loads of a thread's next stage stay in flight in registers.
+//   warp  12    one elected lane issues, per 8 input channels, one N = 64 tcgen05.mma (A_hi from TMEM x [W_hi | W_lo] from
+//               shared memory: hi·hi and hi·lo in one instruction) and one N = 32 (A_lo x W_hi), then commits the stage's
+//               TMEM columns back to the producers through an mbarrier
+//   warps 13-16 epilogue: tcgen05.ld of the three 128 x 32 partial accumulators (a thread = one pixel), sum, + bias, four
+//               32-byte stores = the 128-byte texel of the gather layout; accumulators are double buffered so tile t
+//               drains under tile t+1.
+// W (32 x Cin) is split once per CTA into two resident K-major tiles (UMMA canonical no-swizzle layout, core matrix =
+// 8 channels x 16 bytes), W_lo right behind W_hi so that both form one 64-row B operand.
+// TMEM map (512 columns x 128 lanes, lane = pixel of the tile): [0,192) two accumulator buffers of 96 columns
+// (hi·hi | hi·lo | lo·hi); [192,512) ring of five A stages of 64 columns (32 channels hi | 32 channels lo).
 namespace tc {
-constexpr int kM = 128, kN = 32, kKs = 32, kStagesTc = 3;
-constexpr int kGroups = kStagesTc, kProducerWarps = 4 * kGroups, kMmaWarp = kProducerWarps, kWarps = kProducerWarps + 5;
-// warps 0-11: three producer groups of 128 threads (group g fills ring slot g); warp 12: MMA; warps 13-16: epilogue (warp & 3 = 1,2,3,0)
-constexpr uint32_t kTileBytes = kM * kKs * 4;            // 16 KB: one hi or lo tile of a stage
-constexpr uint32_t kStageBytes = 2 * kTileBytes;
-constexpr uint32_t kLboA = (kM / 8) * 128, kSboA = 128;  // A tile: [k4][pixel group of 8][8 pixels][16 B]
+constexpr int kM = 128, kN = 32, kKs = 32, kStagesTc = 5;
+constexpr int kGroups = 3, kProducerWarps = 4 * kGroups, kMmaWarp = kProducerWarps, kWarps = kProducerWarps + 5;
 constexpr uint32_t kLboB = 128;                          // W tile: [channel group of 8][k4][8 channels][16 B]
 constexpr uint32_t idesc_tf32(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kM >> 4) << 24); }
 constexpr uint32_t kSpinLimit = 1u << 27;
-// Back-to-back tcgen05.mma into ONE accumulator serialise on the accumulate latency (measured: ~143 cycles per 16-cycle
-// M128 N32 K8 instruction). Independent accumulators per tile (3 products x even/odd k8 step) keep several in flight; the
-// epilogue adds them. Two tile buffers of 6 x 32 columns = 384 of the 512 TMEM columns.
-constexpr uint32_t kAccPerTile = 6, kBufCols = kAccPerTile * kN, kTmemCols = 512;
+constexpr uint32_t kAccCols = 3 * kN, kRingCol0 = 2 * kAccCols, kStageCols = 2 * kKs, kTmemCols = 512;
+static_assert(kRingCol0 + kStagesTc * kStageCols <= kTmemCols, "TMEM map");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
@@ -415,9 +417,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
   return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
 }
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-               ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+// D[tmem] (+)= A[tmem] · B[smem]ᵀ: A is 128 lanes x 8 columns of tf32, B a K-major descriptor
+__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+               ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* b) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(b)) : "memory");
@@ -425,21 +428,28 @@ __device__ __forceinline__ void umma_commit(uint64_t* b) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void proxy_fence() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
-  hi = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
-  lo = x - hi;
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                 "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
 __global__ void __launch_bounds__(kWarps * 32, 1)
     k_pwconv_fwd_tc(const float* __restrict__ X, const float* __restrict__ Wm, const float* __restrict__ bias,
                     float* __restrict__ out, int Cin, int Cout, int Cp, int H, int W, int tiles_per_img, int ntiles) {
   extern __shared__ __align__(128) unsigned char sm[];
-  unsigned char* sA = sm;
-  unsigned char* sW = sm + kStagesTc * kStageBytes;
+  unsigned char* sW = sm;
   const uint32_t wbytes = (uint32_t)kN * Cin * 4;                 // one of the two W tiles
   uint64_t* bars = reinterpret_cast<uint64_t*>(sW + 2 * wbytes);
   uint64_t *full = bars, *empty = bars + kStagesTc, *tfull = bars + 2 * kStagesTc, *tempty = bars + 2 * kStagesTc + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStagesTc + 4);
+  float* s_bias = reinterpret_cast<float*>(tmem_slot + 1);        // 32 floats, zero padded
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int HW = H * W, nks = Cin / kKs;
   const uint32_t sboB = (uint32_t)(Cin / 4) * 128;
@@ -453,15 +463,16 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  if (tid < kN) s_bias[tid] = (bias != nullptr && tid < Cout) ? __ldg(bias + tid) : 0.f;
   for (int idx = tid; idx < kN * Cin; idx += kWarps * 32) {
     const int n = idx / Cin, k = idx - n * Cin;
-    float hi, lo;
-    split_tf32(n < Cout ? __ldg(Wm + (size_t)n * Cin + k) : 0.f, hi, lo);
+    const float w = n < Cout ? __ldg(Wm + (size_t)n * Cin + k) : 0.f;
+    const float hi = __uint_as_float(__float_as_uint(w) & 0xffffe000u);
     const uint32_t off = (uint32_t)(n >> 3) * sboB + (uint32_t)(k >> 2) * kLboB + (n & 7) * 16 + (k & 3) * 4;
     *reinterpret_cast<float*>(sW + off) = hi;
-    *reinterpret_cast<float*>(sW + wbytes + off) = lo;
+    *reinterpret_cast<float*>(sW + wbytes + off) = w - hi;
   }
-  proxy_fence();
+  proxy_fence();   // generic-proxy writes of W -> visible to the tensor core's async-proxy reads
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -469,10 +480,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
   const int my_tiles = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
   if (warp < kProducerWarps) {
-    // Producer group g = warp / 4 owns ring slot g and every kGroups-th stage: a warp's chain (wait for the slot, split,
-    // store, proxy fence, arrive) then has kGroups stage times to finish instead of one. A thread owns one pixel and all
-    // 32 input channels of its stage, and keeps the loads of its NEXT stage in flight in registers
-    // (384 threads x up to 64 loads x 4 B = 96 KB per SM; HBM latency x bandwidth needs ~35 KB).
+    // thread = pixel px = TMEM lane (warp & 3 is the lane quarter a warp may touch, and groups start at multiples of 4)
     const int grp = warp >> 2, px = tid & (kM - 1);
     const int total = my_tiles * nks;
     int l_j = grp;                                  // stage index of the load stream (tile-major, then channel block)
@@ -491,24 +499,29 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
       }
       l_j += kGroups;
     };
-    uint32_t s_par = 1;                             // parity of this slot's `empty` barrier
-    unsigned char* const base = sA + grp * kStageBytes + (px >> 3) * kSboA + (px & 7) * 16;
+    int s_j = grp;                                  // stage index of the store stream
+    const uint32_t lane_base = tmem_base + kRingCol0 + ((uint32_t)((warp & 3) * 32) << 16);
     auto store = [&](const float (&v)[kKs]) {
-      mbar_wait(empty + grp, s_par);
-      s_par ^= 1;
+      const int slot = s_j % kStagesTc;
+      mbar_wait(empty + slot, ((s_j / kStagesTc) & 1) ^ 1);   // the MMAs that read this slot have completed
+      tc_fence_after();
+      const uint32_t t0 = lane_base + slot * kStageCols;
 #pragma unroll
-      for (int q = 0; q < kKs / 4; ++q) {
-        float4 hi, lo;
-        split_tf32(v[4 * q + 0], hi.x, lo.x);
-        split_tf32(v[4 * q + 1], hi.y, lo.y);
-        split_tf32(v[4 * q + 2], hi.z, lo.z);
-        split_tf32(v[4 * q + 3], hi.w, lo.w);
-        *reinterpret_cast<float4*>(base + q * kLboA) = hi;
-        *reinterpret_cast<float4*>(base + kTileBytes + q * kLboA) = lo;
+      for (int h = 0; h < kKs / 8; ++h) {
+        uint32_t r[8];   // one 8-register staging set, reused for the lo half (hi is recomputed: one LOP3)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r[i] = __float_as_uint(v[h * 8 + i]) & 0xffffe000u;
+        tmem_st8(t0 + h * 8, r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          r[i] = __float_as_uint(v[h * 8 + i] - __uint_as_float(__float_as_uint(v[h * 8 + i]) & 0xffffe000u));
+        tmem_st8(t0 + kKs + h * 8, r);
       }
-      proxy_fence();   // generic-proxy writes -> visible to the tensor core's async-proxy reads
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(full + grp);
+      if (lane == 0) mbar_arrive(full + slot);
+      s_j += kGroups;
     };
     float b0[kKs], b1[kKs];
     load(b0);
@@ -519,60 +532,51 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
   } else if (warp == kMmaWarp) {
     if (lane == 0) {
       int j = 0;
+      const uint32_t w_addr = smem_u32(sW);
       for (int t = 0; t < my_tiles; ++t) {
         const int buf = t & 1;
-        mbar_wait(tempty + buf, ((t >> 1) & 1) ^ 1);   // the epilogue has drained this accumulator
+        mbar_wait(tempty + buf, ((t >> 1) & 1) ^ 1);   // the epilogue has drained this accumulator buffer
         tc_fence_after();
-        const uint32_t d = tmem_base + buf * kBufCols;
+        const uint32_t d = tmem_base + buf * kAccCols;
         for (int ks = 0; ks < nks; ++ks, ++j) {
           const int slot = j % kStagesTc;
           mbar_wait(full + slot, (j / kStagesTc) & 1);
           tc_fence_after();
-          const uint32_t a_hi = smem_u32(sA + slot * kStageBytes), a_lo = a_hi + kTileBytes;
+          const uint32_t a_hi = tmem_base + kRingCol0 + slot * kStageCols, a_lo = a_hi + kKs;
 #pragma unroll
           for (int k8 = 0; k8 < kKs / 8; ++k8) {
-            const uint32_t aoff = (uint32_t)k8 * 2 * kLboA, boff = (uint32_t)((ks * kKs + k8 * 8) >> 2) * kLboB;
-            const uint64_t ah = umma_desc(a_hi + aoff, kLboA, kSboA), al = umma_desc(a_lo + aoff, kLboA, kSboA);
-            // W_lo sits right behind W_hi with the same channel-group stride: one N = 64 instruction multiplies A_hi by
-            // both (columns 0-31 hi·hi, 32-63 hi·lo), so A_hi is fetched from shared memory once instead of twice
-            const uint64_t bh = umma_desc(smem_u32(sW) + boff, kLboB, sboB);
-            const uint32_t acc = (ks != 0 || k8 >= 2) ? 1u : 0u, dk = d + (k8 & 1) * 3 * kN;
-            umma_tf32(dk, ah, bh, idesc_tf32(2 * kN), acc);
-            umma_tf32(dk + 2 * kN, al, bh, idesc_tf32(kN), acc);
+            const uint64_t b = umma_desc(w_addr + (uint32_t)((ks * kKs + k8 * 8) >> 2) * kLboB, kLboB, sboB);
+            const uint32_t acc = (ks | k8) != 0 ? 1u : 0u;
+            umma_tf32_ts(d, a_hi + k8 * 8, b, idesc_tf32(2 * kN), acc);        // columns 0-31 hi·hi, 32-63 hi·lo
+            umma_tf32_ts(d + 2 * kN, a_lo + k8 * 8, b, idesc_tf32(kN), acc);   // columns 64-95 lo·hi
           }
-          umma_commit(empty + slot);     // stage reusable once these MMAs have read it
+          umma_commit(empty + slot);     // slot reusable once these MMAs have read it
         }
-        umma_commit(tfull + buf);        // accumulator complete
+        umma_commit(tfull + buf);        // accumulators complete
       }
     }
   } else {
     const int q = warp & 3;              // TMEM lane quarter this warp may read
     const int Hp = H + 2, Wp = W + 2;
-    float* s_bias = reinterpret_cast<float*>(tmem_slot + 1);   // 32 floats behind the barriers (zero padded)
-    if (warp == kMmaWarp + 1) s_bias[lane] = (bias != nullptr && lane < Cout) ? __ldg(bias + lane) : 0.f;
-    asm volatile("bar.sync 1, 128;" ::: "memory");             // the four epilogue warps only
     for (int t = 0; t < my_tiles; ++t) {
       const int buf = t & 1;
       const int tile = blockIdx.x + t * gridDim.x;
       mbar_wait(tfull + buf, (t >> 1) & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + buf * kBufCols + ((uint32_t)(q * 32) << 16);
+      const uint32_t taddr = tmem_base + buf * kAccCols + ((uint32_t)(q * 32) << 16);
       float acc[kN];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {          // 16 columns at a time: small terms (lo products) first, hi·hi last
+      for (int h = 0; h < 2; ++h) {          // 16 columns at a time; the small products first, hi·hi last
+        uint32_t r[16];
+        tmem_ld16(taddr + kN + h * 16, r);
 #pragma unroll
-        for (int a = 0; a < (int)kAccPerTile; ++a) {
-          const int which = (a < 4) ? 1 + (a >> 1) + (a & 1) * 3 : (a & 1) * 3;   // blocks 1,4,2,5 (hi·lo, lo·hi), then 0,3 (hi·hi)
-          uint32_t r[16];
-          asm volatile(
-              "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-                "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-              : "r"(taddr + which * kN + h * 16) : "memory");
-          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        for (int i = 0; i < 16; ++i) acc[h * 16 + i] = __uint_as_float(r[i]);
+        tmem_ld16(taddr + 2 * kN + h * 16, r);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) acc[h * 16 + i] = (a == 0) ? __uint_as_float(r[i]) : acc[h * 16 + i] + __uint_as_float(r[i]);
-        }
+        for (int i = 0; i < 16; ++i) acc[h * 16 + i] += __uint_as_float(r[i]);
+        tmem_ld16(taddr + h * 16, r);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[h * 16 + i] += __uint_as_float(r[i]);
       }
       tc_fence_before();
       __syncwarp();
@@ -599,8 +603,8 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
   }
 }
 
-inline size_t smem_bytes(int Cin) { return (size_t)kStagesTc * kStageBytes + 2 * (size_t)kN * Cin * 4 + 256; }
-inline bool usable(int Cin, int Cout) { return Cout <= kN && Cin % kKs == 0 && Cin >= kKs && Cin <= 256; }
+inline size_t smem_bytes(int Cin) { return 2 * (size_t)kN * Cin * 4 + 512; }
+inline bool usable(int Cin, int Cout) { return Cout <= kN && Cin % kKs == 0 && Cin >= kKs && Cin <= 512; }
 }  // namespace tc
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
