@@ -525,24 +525,32 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
     };
     float b0[kKs], b1[kKs];
     load(b0);
-    for (int j = grp; j < total; j += 2 * kGroups) {
-      load(b1); store(b0);
-      if (j + kGroups < total) { load(b0); store(b1); }
+    load(b1);
+    for (int j = grp; j < total; j += 2 * kGroups) {   // a buffer is refilled right after it is stored: both stay in flight
+      store(b0); load(b0);
+      if (j + kGroups < total) { store(b1); load(b1); }
     }
   } else if (warp == kMmaWarp) {
-    if (lane == 0) {
-      int j = 0;
-      const uint32_t w_addr = smem_u32(sW);
-      for (int t = 0; t < my_tiles; ++t) {
-        const int buf = t & 1;
-        mbar_wait(tempty + buf, ((t >> 1) & 1) ^ 1);   // the epilogue has drained this accumulator buffer
+    // The whole warp walks the loop with warp-uniform values (TMEM base re-broadcast with a shuffle so that the compiler
+    // can keep descriptors in uniform registers) and one elected lane issues. With the loop under `if (lane == 0)` every
+    // UTCHMMA was wrapped in an ELECT / 4 x R2UR / branch sequence: ~300 cycles per 8-channel step, which alone bounded
+    // the kernel at 165 us (measured).
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    uint32_t leader;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(leader));
+    int j = 0;
+    const uint32_t w_addr = smem_u32(sW);
+    for (int t = 0; t < my_tiles; ++t) {
+      const int buf = t & 1;
+      mbar_wait(tempty + buf, ((t >> 1) & 1) ^ 1);   // the epilogue has drained this accumulator buffer
+      tc_fence_after();
+      const uint32_t d = tb + buf * kAccCols;
+      for (int ks = 0; ks < nks; ++ks, ++j) {
+        const int slot = j % kStagesTc;
+        mbar_wait(full + slot, (j / kStagesTc) & 1);
         tc_fence_after();
-        const uint32_t d = tmem_base + buf * kAccCols;
-        for (int ks = 0; ks < nks; ++ks, ++j) {
-          const int slot = j % kStagesTc;
-          mbar_wait(full + slot, (j / kStagesTc) & 1);
-          tc_fence_after();
-          const uint32_t a_hi = tmem_base + kRingCol0 + slot * kStageCols, a_lo = a_hi + kKs;
+        const uint32_t a_hi = tb + kRingCol0 + slot * kStageCols, a_lo = a_hi + kKs;
+        if (leader) {
 #pragma unroll
           for (int k8 = 0; k8 < kKs / 8; ++k8) {
             const uint64_t b = umma_desc(w_addr + (uint32_t)((ks * kKs + k8 * 8) >> 2) * kLboB, kLboB, sboB);
@@ -552,8 +560,10 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
           }
           umma_commit(empty + slot);     // slot reusable once these MMAs have read it
         }
-        umma_commit(tfull + buf);        // accumulators complete
+        __syncwarp();
       }
+      if (leader) umma_commit(tfull + buf);   // accumulators complete
+      __syncwarp();
     }
   } else {
     const int q = warp & 3;              // TMEM lane quarter this warp may read
