@@ -8,11 +8,12 @@
 //   backward (data)  dX[n,k,y,x]         = Σ_c W[c,k] · G[n, y+1, x+1, c]
 //   backward (weight) dW[c,k] = Σ_{n,y,x} G[n,y+1,x+1,c] · X[n,k,y,x],   db[c] = Σ G[n,y+1,x+1,c]
 //
-// All three are fp32 FMA chains in a fixed order (k ascending; partial sums of the weight gradient merged in worker
-// order): deterministic, and within 1e-6 of ATen's fp32 convolution. The work is GEMM shaped (M = pixels, N = 32,
-// K = 256) but stays on the FMA pipe as packed FFMA2: the parity bar is the fp32 oracle, and single-pass TF32 tensor-core
-// products are 1e-3 away from it (a 3xTF32 tcgen05 version is the listed follow-up). Bounds: forward and
-// backward-data read or write the (B·V,256,H,W) tensor once (HBM floor) and issue 2·Cin·Cout flops per pixel (FFMA2 floor).
+// The work is GEMM shaped (M = pixels, N = 32, K = 256). The forward runs on the tcgen05 tensor cores with a three-product
+// TF32 split that keeps fp32 accuracy (namespace tc below; the parity bar is the fp32 oracle and single-pass TF32 is 1e-3
+// away from it); shapes it does not cover, and the two backward kernels, are fp32 FMA chains in a fixed order (k ascending;
+// partial sums of the weight gradient merged in worker order) as packed FFMA2. Everything is deterministic and within
+// 2e-6 of ATen's fp32 convolution. Bounds: forward and backward-data read or write the (B·V,256,H,W) tensor once (HBM
+// floor) and issue 2·Cin·Cout flops per pixel.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -613,6 +614,175 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
   }
 }
 
+// ---- backward w.r.t. the input on the tensor cores -------------------------------------------------------------------
+// dX[px][k] = Σ_c G[px][c] · W[c][k]: M = 128 pixels, N = Cin (<= 256), K = 32 output channels (zero padded). The same
+// 3xTF32 split; here the accumulator is the big thing (128 x 256 fp32 = 256 TMEM columns, double buffered = all 512), so
+// the small A operand (the pixel tile of the hwcp gradient map, already K-major: 128 contiguous bytes per pixel) goes
+// through shared memory as UMMA canonical tiles and W^T (hi and lo, 64 KB) stays resident.
+//   warps 0-7   two producer groups (thread = pixel) alternating tiles: 8 x LDG.128 of the pixel's texel, split, STS
+//   warp  8     12 tcgen05.mma (N = Cin, K = 8) per tile into one accumulator: lo·hi, hi·lo, hi·hi
+//   warps 9-16  epilogue: a thread owns a pixel and half of the input channels; tcgen05.ld, then one coalesced 128-byte
+//               store per channel and warp into the channel-planar gradient.
+constexpr int kBdStages = 3, kBdProducerWarps = 8, kBdMmaWarp = 8, kBdWarps = 17;
+constexpr uint32_t kBdLboA = (kM / 8) * 128, kBdSboA = 128, kBdTile = kM * kN * 4;   // A: [c4][pixel group][8 px][16 B]
+constexpr uint32_t kBdLboB = 128, kBdSboB = (kN / 4) * 128;                          // W^T: [k group of 8][c4][8 k][16 B]
+
+__device__ __forceinline__ void umma_tf32_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
+      "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(kBdWarps * 32, 1)
+    k_pwconv_bwd_data_tc(const float* __restrict__ G, const float* __restrict__ Wm, float* __restrict__ dX, int Cin,
+                         int Cout, int Cp, int H, int W, int tiles_per_img, int ntiles) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  unsigned char* sA = sm;                                        // [kBdStages][hi 16 KB | lo 16 KB]
+  unsigned char* sW = sm + kBdStages * 2 * kBdTile;              // W^T hi (Cin x 32) then lo
+  const uint32_t wbytes = (uint32_t)Cin * kN * 4;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sW + 2 * wbytes);
+  uint64_t *full = bars, *empty = bars + kBdStages, *tfull = bars + 2 * kBdStages, *tempty = bars + 2 * kBdStages + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kBdStages + 4);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int HW = H * W, Hp = H + 2, Wp = W + 2;
+
+  if (tid == 0) {
+    for (int s = 0; s < kBdStages; ++s) { mbar_init(full + s, 4); mbar_init(empty + s, 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kBdMmaWarp) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (int idx = tid; idx < Cin * kN; idx += kBdWarps * 32) {   // idx = c * Cin + k: coalesced reads of W (Cout, Cin)
+    const int c = idx / Cin, k = idx - c * Cin;
+    const float w = c < Cout ? __ldg(Wm + (size_t)c * Cin + k) : 0.f;
+    const float hi = __uint_as_float(__float_as_uint(w) & 0xffffe000u);
+    const uint32_t off = (uint32_t)(k >> 3) * kBdSboB + (uint32_t)(c >> 2) * kBdLboB + (k & 7) * 16 + (c & 3) * 4;
+    *reinterpret_cast<float*>(sW + off) = hi;
+    *reinterpret_cast<float*>(sW + wbytes + off) = w - hi;
+  }
+  proxy_fence();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int my_tiles = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (warp < kBdProducerWarps) {
+    const int grp = warp >> 2, px = tid & (kM - 1);
+    unsigned char* const base0 = sA + (px >> 3) * kBdSboA + (px & 7) * 16;
+    float4 v[kN / 4];
+    auto load = [&](int t) {
+      if (t >= my_tiles) return;
+      const int tile = blockIdx.x + t * gridDim.x;
+      const int bv = tile / tiles_per_img, p = (tile - bv * tiles_per_img) * kM + px;
+      if (p < HW) {
+        const int y = p / W, x = p - y * W;
+        const float* src = G + (((size_t)bv * Hp + y + 1) * Wp + x + 1) * Cp;
+#pragma unroll
+        for (int q = 0; q < kN / 4; ++q) v[q] = ldg128_stream(src + q * 4);
+      } else {
+#pragma unroll
+        for (int q = 0; q < kN / 4; ++q) v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    };
+    load(grp);
+    for (int t = grp; t < my_tiles; t += 2) {
+      const int slot = t % kBdStages;
+      mbar_wait(empty + slot, ((t / kBdStages) & 1) ^ 1);
+      unsigned char* const base = base0 + slot * 2 * kBdTile;
+#pragma unroll
+      for (int q = 0; q < kN / 4; ++q) {
+        float4 hi, lo;
+        hi.x = __uint_as_float(__float_as_uint(v[q].x) & 0xffffe000u); lo.x = v[q].x - hi.x;
+        hi.y = __uint_as_float(__float_as_uint(v[q].y) & 0xffffe000u); lo.y = v[q].y - hi.y;
+        hi.z = __uint_as_float(__float_as_uint(v[q].z) & 0xffffe000u); lo.z = v[q].z - hi.z;
+        hi.w = __uint_as_float(__float_as_uint(v[q].w) & 0xffffe000u); lo.w = v[q].w - hi.w;
+        *reinterpret_cast<float4*>(base + q * kBdLboA) = hi;
+        *reinterpret_cast<float4*>(base + kBdTile + q * kBdLboA) = lo;
+      }
+      proxy_fence();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full + slot);
+      load(t + 2);
+    }
+  } else if (warp == kBdMmaWarp) {
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    uint32_t leader;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(leader));
+    const uint32_t w_addr = smem_u32(sW), a_addr = smem_u32(sA);
+    const uint32_t idesc = idesc_tf32(Cin);
+    for (int t = 0; t < my_tiles; ++t) {
+      const int buf = t & 1, slot = t % kBdStages;
+      mbar_wait(tempty + buf, ((t >> 1) & 1) ^ 1);
+      mbar_wait(full + slot, (t / kBdStages) & 1);
+      tc_fence_after();
+      if (leader) {
+        const uint32_t d = tb + buf * 256;
+#pragma unroll
+        for (int k8 = 0; k8 < kN / 8; ++k8) {
+          const uint64_t ah = umma_desc(a_addr + slot * 2 * kBdTile + k8 * 2 * kBdLboA, kBdLboA, kBdSboA);
+          const uint64_t al = umma_desc(a_addr + slot * 2 * kBdTile + kBdTile + k8 * 2 * kBdLboA, kBdLboA, kBdSboA);
+          const uint64_t bh = umma_desc(w_addr + k8 * 2 * kBdLboB, kBdLboB, kBdSboB);
+          const uint64_t bl = umma_desc(w_addr + wbytes + k8 * 2 * kBdLboB, kBdLboB, kBdSboB);
+          umma_tf32_ss(d, al, bh, idesc, k8 != 0 ? 1u : 0u);
+          umma_tf32_ss(d, ah, bl, idesc, 1u);
+          umma_tf32_ss(d, ah, bh, idesc, 1u);
+        }
+        umma_commit(empty + slot);
+        umma_commit(tfull + buf);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int e = warp - (kBdMmaWarp + 1);            // 0..7
+    const int q = warp & 3, half = e >> 2;            // TMEM lane quarter, and which half of the input channels
+    const int kper = (Cin + 1) / 2;                   // channels [half*kper, min(Cin, (half+1)*kper))
+    for (int t = 0; t < my_tiles; ++t) {
+      const int buf = t & 1;
+      const int tile = blockIdx.x + t * gridDim.x;
+      const int bv = tile / tiles_per_img, p = (tile - bv * tiles_per_img) * kM + q * 32 + lane;
+      mbar_wait(tfull + buf, (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
+      float* dst = dX + (size_t)bv * Cin * HW + p;
+      const int k_end = min(Cin, (half + 1) * kper);
+      for (int k0 = half * kper; k0 < k_end; k0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(taddr + k0, r);     // columns beyond Cin are never read back: k0 + i < k_end below
+        if (p < HW) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (k0 + i < k_end) __stcs(dst + (size_t)(k0 + i) * HW, __uint_as_float(r[i]));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty + buf);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kBdMmaWarp) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+  }
+}
+inline size_t bd_smem_bytes(int Cin) { return (size_t)kBdStages * 2 * kBdTile + 2 * (size_t)Cin * kN * 4 + 512; }
+inline bool bd_usable(int Cin, int Cout) { return Cout <= kN && Cin % 64 == 0 && Cin >= 64 && Cin <= 256; }
+
 inline size_t smem_bytes(int Cin) { return 2 * (size_t)kN * Cin * 4 + 512; }
 inline bool usable(int Cin, int Cout) { return Cout <= kN && Cin % kKs == 0 && Cin >= kKs && Cin <= 512; }
 }  // namespace tc
@@ -673,6 +843,15 @@ cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* 
 cudaError_t launch_pwconv_bwd_data(const float* grad_hwcp, const float* weight, float* grad_x, int BV, int Cin,
                                    int Cout, int H, int W, cudaStream_t st) {
   const int Cp = padded_channels(Cout), HW = H * W;
+  if (tc::bd_usable(Cin, Cout) && !force_ffma()) {
+    const int tiles_per_img = (HW + tc::kM - 1) / tc::kM, ntiles = BV * tiles_per_img;
+    const int smem = (int)tc::bd_smem_bytes(Cin);
+    cudaError_t e = cudaFuncSetAttribute(tc::k_pwconv_bwd_data_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    tc::k_pwconv_bwd_data_tc<<<ntiles < 148 ? ntiles : 148, tc::kBdWarps * 32, smem, st>>>(grad_hwcp, weight, grad_x, Cin, Cout,
+                                                                                         Cp, H, W, tiles_per_img, ntiles);
+    return cudaGetLastError();
+  }
   dim3 grid((unsigned)((HW + kPx - 1) / kPx), (unsigned)BV, (unsigned)((Cin + kKn - 1) / kKn));
   const bool vec = (HW % 4 == 0) && aligned16(grad_x);
   auto kern = vec ? k_pwconv_bwd_data<true> : k_pwconv_bwd_data<false>;
