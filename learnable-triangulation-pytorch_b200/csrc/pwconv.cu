@@ -757,15 +757,20 @@ __global__ void __launch_bounds__(kBdWarps * 32, 1)
       mbar_wait(tfull + buf, (t >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
-      float* dst = dX + (size_t)bv * Cin * HW + p;
-      const int k_end = min(Cin, (half + 1) * kper);
-      for (int k0 = half * kper; k0 < k_end; k0 += 32) {
+      // Cin % 64 == 0 (bd_usable): each half is a whole number of 32-column loads, no per-channel bound check; the
+      // store address advances by one plane per channel (a bound check + 64-bit multiply per store made this epilogue
+      // 2600 instructions per warp and tile, and the kernel instruction bound at 235 us)
+      float* q = dX + ((size_t)bv * Cin + half * kper) * HW + p;
+      const size_t plane = (size_t)HW;
+      for (int k0 = 0; k0 < kper; k0 += 32) {
         uint32_t r[32];
-        tmem_ld32(taddr + k0, r);     // columns beyond Cin are never read back: k0 + i < k_end below
+        tmem_ld32(taddr + half * kper + k0, r);
         if (p < HW) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (k0 + i < k_end) __stcs(dst + (size_t)(k0 + i) * HW, __uint_as_float(r[i]));
+          for (int i = 0; i < 32; ++i) {
+            *q = __uint_as_float(r[i]);   // write-back: L2 merges a plane's neighbouring tiles
+            q += plane;
+          }
         }
       }
       tc_fence_before();
