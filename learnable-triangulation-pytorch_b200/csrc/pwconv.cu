@@ -788,6 +788,218 @@ __global__ void __launch_bounds__(kBdWarps * 32, 1)
 inline size_t bd_smem_bytes(int Cin) { return (size_t)kBdStages * 2 * kBdTile + 2 * (size_t)Cin * kN * 4 + 512; }
 inline bool bd_usable(int Cin, int Cout) { return Cout <= kN && Cin % 64 == 0 && Cin >= 64 && Cin <= 256; }
 
+// ---- backward w.r.t. the weight on the tensor cores ------------------------------------------------------------------
+// dW[c][k] = Σ_p G[p][c] · X[k][p], computed as D[k][c]: M = 128 input channels per block (Cin / 128 blocks), N = 32 output
+// channels, K = pixels. A = X rows (pixel-contiguous = K-major as stored), B = the gradient tile transposed to channel rows.
+// Persistent CTAs walk 32-pixel chunks and keep their partial dW in TMEM until the end; the per-CTA partials go to the same
+// workspace as the FFMA kernel's and are merged in CTA order by k_pw_reduce_partials (deterministic).
+//   warps 0-7   fill a 4-deep raw ring with 16-byte cp.async three chunks ahead (completion counted by an mbarrier through
+//               cp.async.mbarrier.arrive.noinc), then act as converters, thread = input channel row = TMEM lane:
+//               8 x LDS.128 of the row (144-byte pitch: conflict free),
+//               split, tcgen05.st of hi and lo into the A ring in tensor memory; the same threads transpose + split the
+//               gradient texels into the UMMA canonical B tile ([G_hi | G_lo] as 64 rows) and keep the bias-gradient sums
+//   warp  8     per 8 pixels and channel block: one N = 64 MMA (X_hi x [G_hi | G_lo]) and one N = 32 (X_lo x G_hi)
+// TMEM map: [0,192) accumulators of the two channel blocks (hi·hi | hi·lo | lo·hi), [192,448) two A slots of 2 x 64 columns.
+constexpr int kBwPx = 32, kBwRawStages = 4, kBwSlots = 2, kBwConvWarps = 8, kBwMmaWarp = 8, kBwWarps = 9;
+constexpr uint32_t kBwRowPitch = 144;                                   // raw X row: 128 B + 16 B pad
+constexpr uint32_t kBwRawX = 256 * kBwRowPitch, kBwRawBytes = kBwRawX + kBwPx * 128;   // 36,864 + 4,096
+constexpr uint32_t kBwBTile = 2 * kN * kBwPx * 4;                        // 8 KB: 64 rows x 32 pixels
+constexpr uint32_t kBwLboB = 128, kBwSboB = (kBwPx / 4) * 128;           // [channel group of 8][p4][8 channels][16 B]
+constexpr uint32_t kBwAccCols = 3 * kN, kBwRing0 = 2 * kBwAccCols, kBwSlotCols = 2 * 2 * kBwPx;
+
+__global__ void __launch_bounds__(kBwWarps * 32, 1)
+    k_pwconv_bwd_weight_tc(const float* __restrict__ X, const float* __restrict__ G, float* __restrict__ part_w,
+                           float* __restrict__ part_b, int Cin, int Cp, int H, int W, int chunks_per_img, int nchunks,
+                           int CinPad) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  unsigned char* sRaw = sm;                                              // [kBwRawStages][X rows | G texels]
+  unsigned char* sB = sm + kBwRawStages * kBwRawBytes;                   // [kBwSlots][8 KB]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + kBwSlots * kBwBTile);
+  uint64_t *full_raw = bars, *empty_raw = bars + kBwRawStages, *full_mma = bars + 2 * kBwRawStages,
+           *empty_mma = full_mma + kBwSlots, *done = empty_mma + kBwSlots;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  float* s_db = reinterpret_cast<float*>(tmem_slot + 1);                 // 32 floats
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int HW = H * W, Hp = H + 2, Wp = W + 2;
+  const int nblk = Cin / kM;                                            // 1 or 2 channel blocks
+
+  if (tid == 0) {
+    for (int s = 0; s < kBwRawStages; ++s) { mbar_init(full_raw + s, kBwConvWarps * 32); mbar_init(empty_raw + s, kBwConvWarps); }
+    for (int s = 0; s < kBwSlots; ++s) { mbar_init(full_mma + s, kBwConvWarps); mbar_init(empty_mma + s, 1); }
+    mbar_init(done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kBwMmaWarp) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid < kN) s_db[tid] = 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int my_chunks = (int)blockIdx.x < nchunks ? (nchunks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (warp == kBwMmaWarp) {
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    uint32_t leader;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(leader));
+    const uint32_t b_addr = smem_u32(sB);
+    for (int i = 0; i < my_chunks; ++i) {
+      const int slot = i % kBwSlots;
+      mbar_wait(full_mma + slot, (i / kBwSlots) & 1);
+      tc_fence_after();
+      if (leader) {
+#pragma unroll
+        for (int k8 = 0; k8 < kBwPx / 8; ++k8) {
+          const uint64_t b = umma_desc(b_addr + slot * kBwBTile + k8 * 2 * kBwLboB, kBwLboB, kBwSboB);
+          const uint32_t acc = (i | k8) != 0 ? 1u : 0u;
+          for (int mb = 0; mb < nblk; ++mb) {
+            const uint32_t d = tb + mb * kBwAccCols;
+            const uint32_t a_hi = tb + kBwRing0 + slot * kBwSlotCols + mb * 2 * kBwPx + k8 * 8, a_lo = a_hi + kBwPx;
+            umma_tf32_ts(d, a_hi, b, idesc_tf32(2 * kN), acc);        // columns 0-31 hi·hi, 32-63 hi·lo
+            umma_tf32_ts(d + 2 * kN, a_lo, b, idesc_tf32(kN), acc);   // columns 64-95 lo·hi
+          }
+        }
+        umma_commit(empty_mma + slot);
+        if (i == my_chunks - 1) umma_commit(done);
+      }
+      __syncwarp();
+    }
+  } else {
+    // converters: thread = input channel row `tid` (< Cin) = TMEM lane tid & 127 of channel block tid >> 7
+    const int mb = tid >> 7;
+    const bool row_ok = tid < Cin;
+    const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + kBwRing0 + mb * 2 * kBwPx;
+    const int gp = tid >> 3, gc4 = tid & 7;           // gradient texel duty: pixel gp, channels 4*gc4..+3
+    float bacc[4] = {0.f, 0.f, 0.f, 0.f};
+    // raw ring fill: 16-byte cp.async, lanes along the pixels of a row (a warp instruction = four whole 128-byte lines);
+    // each thread posts a no-increment arrive on the stage's mbarrier that fires when ITS copies have landed. (One warp
+    // issuing 288 cp.async.bulk of 128 B per chunk instead: 8.8 us per chunk, measured.)
+    auto issue = [&](int i) {
+      if (i >= my_chunks) return;
+      const int s = i % kBwRawStages;
+      mbar_wait(empty_raw + s, ((i / kBwRawStages) & 1) ^ 1);
+      const int chunk = blockIdx.x + i * gridDim.x;
+      const int bv = chunk / chunks_per_img, p0 = (chunk - bv * chunks_per_img) * kBwPx;
+      float* raw = reinterpret_cast<float*>(sRaw + s * kBwRawBytes);
+      const float* xs = X + ((size_t)bv * Cin + (tid >> 3)) * HW + p0 + (tid & 7) * 4;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int row = (tid >> 3) + 32 * j;
+        if (row < Cin) cp_async16(raw + row * (kBwRowPitch / 4) + (tid & 7) * 4, xs + (size_t)(32 * j) * HW, true);
+      }
+      const int p = p0 + gp, y = p / W, x = p - y * W;   // HW % 32 == 0: every pixel of the chunk exists
+      cp_async16(raw + kBwRawX / 4 + gp * 32 + gc4 * 4, G + (((size_t)bv * Hp + y + 1) * Wp + x + 1) * Cp + gc4 * 4, true);
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(full_raw + s)) : "memory");
+    };
+    issue(0); issue(1); issue(2);
+    for (int i = 0; i < my_chunks; ++i) {
+      const int s = i % kBwRawStages, slot = i % kBwSlots;
+      issue(i + kBwRawStages - 1);
+      mbar_wait(full_raw + s, (i / kBwRawStages) & 1);
+      const unsigned char* raw = sRaw + s * kBwRawBytes;
+      float4 xr[kBwPx / 4];
+#pragma unroll
+      for (int q = 0; q < kBwPx / 4; ++q)
+        xr[q] = row_ok ? *reinterpret_cast<const float4*>(raw + tid * kBwRowPitch + q * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 g = *reinterpret_cast<const float4*>(raw + kBwRawX + gp * 128 + gc4 * 16);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_raw + s);      // raw stage consumed (values are in registers)
+      mbar_wait(empty_mma + slot, ((i / kBwSlots) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t t0 = lane_base + slot * kBwSlotCols;
+#pragma unroll
+      for (int q = 0; q < kBwPx / 8; ++q) {
+        const float v[8] = {xr[2 * q].x, xr[2 * q].y, xr[2 * q].z, xr[2 * q].w,
+                            xr[2 * q + 1].x, xr[2 * q + 1].y, xr[2 * q + 1].z, xr[2 * q + 1].w};
+        uint32_t r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = __float_as_uint(v[j]) & 0xffffe000u;
+        tmem_st8(t0 + q * 8, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = __float_as_uint(v[j] - __uint_as_float(__float_as_uint(v[j]) & 0xffffe000u));
+        tmem_st8(t0 + kBwPx + q * 8, r);
+      }
+      {
+        // B tile: element (row n = channel (+32 for lo), pixel p) at (n>>3)*SBO + (p>>2)*LBO + (n&7)*16 + (p&3)*4
+        unsigned char* bt = sB + slot * kBwBTile + (uint32_t)(gp >> 2) * kBwLboB + (gp & 3) * 4;
+        const float gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int n = gc4 * 4 + j;
+          const float hi = __uint_as_float(__float_as_uint(gv[j]) & 0xffffe000u);
+          *reinterpret_cast<float*>(bt + (uint32_t)(n >> 3) * kBwSboB + (n & 7) * 16) = hi;
+          *reinterpret_cast<float*>(bt + (uint32_t)((n + kN) >> 3) * kBwSboB + (n & 7) * 16) = gv[j] - hi;
+          bacc[j] += gv[j];
+        }
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      proxy_fence();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full_mma + slot);
+    }
+    // epilogue: this thread's dW row (input channel tid, all 32 output channels) from the three partial accumulators
+    if (my_chunks > 0) {
+      mbar_wait(done, 0);
+      tc_fence_after();
+    }
+    if (row_ok) {
+      const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + mb * kBwAccCols;
+      float* dst = part_w + ((size_t)blockIdx.x * CinPad + tid) * Cp;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        float acc[16];
+        uint32_t r[16];
+        if (my_chunks > 0) {
+          tmem_ld16(taddr + kN + h * 16, r);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(r[j]);
+          tmem_ld16(taddr + 2 * kN + h * 16, r);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc[j] += __uint_as_float(r[j]);
+          tmem_ld16(taddr + h * 16, r);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc[j] += __uint_as_float(r[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 16; j += 4)
+          *reinterpret_cast<float4*>(dst + h * 16 + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+      }
+    }
+    // bias gradient: 32 threads share a channel quad; fixed-order tree through shared memory would need 1 KB, the sums
+    // are added with shared atomics instead and the order across the CTA's 32 pixel lanes is fixed by the barrier below
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float v = bacc[j];                              // lanes with equal (lane & 7): xor-reduce over lane bits 3,4
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      bacc[j] = v;
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    for (int w = 0; w < kBwConvWarps; ++w) {          // warps add in warp order: deterministic
+      if (warp == w && lane < 8) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) s_db[lane * 4 + j] += bacc[j];
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+    }
+    if (tid < kN) part_b[(size_t)blockIdx.x * Cp + tid] = s_db[tid];
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kBwMmaWarp) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+  }
+}
+inline size_t bw_smem_bytes() { return (size_t)kBwRawStages * kBwRawBytes + kBwSlots * kBwBTile + 512; }
+inline bool bw_usable(int Cin, int Cout, int HW) { return Cout <= kN && (Cin == 128 || Cin == 256) && HW % kBwPx == 0; }
+
 inline size_t smem_bytes(int Cin) { return 2 * (size_t)kN * Cin * 4 + 512; }
 inline bool usable(int Cin, int Cout) { return Cout <= kN && Cin % kKs == 0 && Cin >= kKs && Cin <= 512; }
 }  // namespace tc
@@ -805,7 +1017,7 @@ bool force_ffma() {
   return v;
 }
 
-int weight_workers(int BV, int H, int W) {
+int weight_workers(int BV, int H, int W) {   // an upper bound for both weight-gradient kernels (the tcgen05 one uses <= 148)
   const long long total = (long long)BV * ((H * W + kWgPx - 1) / kWgPx);
   return (int)(total < kWeightWorkers ? total : kWeightWorkers);
 }
@@ -874,6 +1086,20 @@ cudaError_t launch_pwconv_bwd_weight(const float* x, const float* grad_hwcp, flo
   const int CinPad = ((Cin + kKn - 1) / kKn) * kKn;
   const int nchunk = (HW + kWgPx - 1) / kWgPx, total = BV * nchunk;
   const int nw = weight_workers(BV, H, W);
+  if (tc::bw_usable(Cin, Cout, HW) && aligned16(x) && !force_ffma()) {
+    const int chunks_per_img = HW / tc::kBwPx, nchunks = BV * chunks_per_img;
+    const int nctas = nchunks < 148 ? nchunks : 148;
+    float* pw = static_cast<float*>(ws);
+    float* pb = pw + (size_t)nctas * CinPad * Cp;
+    const int smem = (int)tc::bw_smem_bytes();
+    cudaError_t e = cudaFuncSetAttribute(tc::k_pwconv_bwd_weight_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    tc::k_pwconv_bwd_weight_tc<<<nctas, tc::kBwWarps * 32, smem, st>>>(x, grad_hwcp, pw, pb, Cin, Cp, H, W, chunks_per_img,
+                                                                      nchunks, CinPad);
+    dim3 rg((unsigned)(Cin + 1), (unsigned)(Cp / 32));
+    k_pw_reduce_partials<<<rg, 256, 0, st>>>(pw, pb, grad_weight, grad_bias, Cin, Cout, Cp, CinPad, nctas);
+    return cudaGetLastError();
+  }
   float* part_w = static_cast<float*>(ws);
   float* part_b = part_w + (size_t)nw * CinPad * Cp;
   dim3 grid((unsigned)nw, (unsigned)(CinPad / kKn), (unsigned)(Cp / kCo));
