@@ -8,12 +8,12 @@
 //   backward (data)  dX[n,k,y,x]         = Σ_c W[c,k] · G[n, y+1, x+1, c]
 //   backward (weight) dW[c,k] = Σ_{n,y,x} G[n,y+1,x+1,c] · X[n,k,y,x],   db[c] = Σ G[n,y+1,x+1,c]
 //
-// The work is GEMM shaped (M = pixels, N = 32, K = 256). The forward runs on the tcgen05 tensor cores with a three-product
-// TF32 split that keeps fp32 accuracy (namespace tc below; the parity bar is the fp32 oracle and single-pass TF32 is 1e-3
-// away from it); shapes it does not cover, and the two backward kernels, are fp32 FMA chains in a fixed order (k ascending;
-// partial sums of the weight gradient merged in worker order) as packed FFMA2. Everything is deterministic and within
-// 2e-6 of ATen's fp32 convolution. Bounds: forward and backward-data read or write the (B·V,256,H,W) tensor once (HBM
-// floor) and issue 2·Cin·Cout flops per pixel.
+// The work is GEMM shaped (M = pixels, N = 32, K = 256). At the reference's shape all three kernels run on the tcgen05
+// tensor cores with a three-product TF32 split that keeps fp32 accuracy (namespace tc below; the parity bar is the fp32
+// oracle and single-pass TF32 is 1e-3 away from it); shapes they do not cover run fp32 FMA chains in a fixed order as
+// packed FFMA2 (k_pwconv_fwd / _bwd_data / _bwd_weight). Everything is deterministic (the weight gradient's per-CTA partial
+// sums are merged in CTA order) and within 2e-6 of ATen's fp32 convolution. Bounds: each kernel reads or writes the
+// (B·V,256,H,W) tensor once (HBM floor) and issues 2·Cin·Cout flops per pixel.
 #include <stdlib.h>
 
 #include "common.cuh"
