@@ -344,6 +344,46 @@ class E2EStep:
 # ---------------------------------------------------------------------------------------------------------------------
 # CPU reference arm (oracle port of the reference's torch CPU path): one volume (B=1) per step
 # ---------------------------------------------------------------------------------------------------------------------
+def bench_process_features(step, w, B, peak, iters=20):
+    """K7 at this workload's shape: (B*V, 256, H, W) planar features -> the gather layout K1 reads (and back): CUDA events
+    around `iters` launches of each entry point on torch's current stream; 256 input channels as in the reference."""
+    L = step.L
+    BV, C, H, W, Cin = B * w["V"], w["C"], w["H"], w["W"], 256
+    dev = step.feat.device
+    x = torch.randn(BV, Cin, H, W, device=dev)
+    wt = torch.randn(C, Cin, device=dev) / 16.0
+    bias = torch.randn(C, device=dev)
+    n_hwcp = L.lt_feat_layout_elems(BV, C, H, W)
+    out, g = torch.empty(n_hwcp, device=dev), torch.randn(n_hwcp, device=dev)
+    gx, gw, gb = torch.empty_like(x), torch.empty_like(wt), torch.empty_like(bias)
+    ws = torch.empty(max(L.lt_pwconv_ws_bytes(BV, Cin, C, H, W), 4) // 4, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    calls = {
+        "fwd": lambda: L.lt_pwconv_fwd(x.data_ptr(), wt.data_ptr(), bias.data_ptr(), out.data_ptr(), ws.data_ptr(), BV, Cin,
+                                       C, H, W, st),
+        "bwd_data": lambda: L.lt_pwconv_bwd_data(g.data_ptr(), wt.data_ptr(), gx.data_ptr(), BV, Cin, C, H, W, st),
+        "bwd_weight": lambda: L.lt_pwconv_bwd_weight(x.data_ptr(), g.data_ptr(), gw.data_ptr(), gb.data_ptr(), ws.data_ptr(),
+                                                     BV, Cin, C, H, W, st),
+    }
+    nbytes = (x.numel() + n_hwcp) * 4
+    res = {"shape": "B*V=%d maps, %d -> %d channels, %dx%d" % (BV, Cin, C, H, W), "algorithmic_bytes": nbytes,
+           "flops": 2.0 * BV * H * W * Cin * C, "kernels": {}}
+    for name, fn in calls.items():
+        for _ in range(3):
+            rc = fn()
+            if rc != 0:
+                raise RuntimeError("%s returned %d" % (name, rc))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); a.record()
+        for _ in range(iters):
+            fn()
+        b.record(); torch.cuda.synchronize()
+        us = a.elapsed_time(b) / iters * 1e3
+        res["kernels"][name] = {"us": round(us, 1), "gbs": round(nbytes / us * 1e-3, 1),
+                                "frac": round(nbytes / us * 1e-3 / peak, 4)}
+    return res
+
+
 def cpu_reference_step(w, seed=0, cache={}):
     """fwd+bwd of unproject_heatmaps and integrate_tensor_3d_with_coordinates for ONE batch item with the oracle's
     restatement of mvn/utils/op.py (same ATen calls as the reference) on all host cores. Returns seconds."""
@@ -515,6 +555,14 @@ def main():
             roofline["traffic"] = json.load(open(traffic_file)).get(args.workload, {}).get(top)
         except Exception:
             pass
+
+    # SURVEY 8(f) row 4, reported beside the path (never part of `value`): K7 = the process_features 1x1 convolution that
+    # feeds K1 (triangulation.py:238-240, 344-346) at this workload's map count, 256 -> C channels, through the C ABI.
+    if rank == 0 and world == 1 and not args.no_e2e:
+        try:
+            roofline["next_rows"] = {"k7_process_features": bench_process_features(step, w, B, peak)}
+        except Exception as exc:  # a side measurement must never cost the bench line
+            roofline["next_rows"] = {"k7_process_features": {"error": repr(exc)[:200]}}
 
     e2e = None
     if not args.no_e2e:

@@ -493,7 +493,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
       if (p < HW) {
         const float* src = X + ((size_t)bv * Cin + ks * kKs) * HW + p;
 #pragma unroll
-        for (int i = 0; i < kKs; ++i) v[i] = __ldg(src + (size_t)i * HW);
+        for (int i = 0; i < kKs; ++i) v[i] = __ldg(src + (size_t)i * HW);   // ld.cg / .cs / .lu variants: 146-149 us, no difference (measured)
       } else {
 #pragma unroll
         for (int i = 0; i < kKs; ++i) v[i] = 0.f;
