@@ -391,6 +391,7 @@ __global__ void __launch_bounds__(256) k_pw_reduce_partials(const float* __restr
 namespace tc {
 constexpr int kM = 128, kN = 32, kKs = 32, kStagesTc = 5;
 constexpr int kGroups = 3, kProducerWarps = 4 * kGroups, kMmaWarp = kProducerWarps, kWarps = kProducerWarps + 5;
+constexpr int kRawDepth = 3;   // raw stages in flight per producer group (16 KB each)
 constexpr uint32_t kLboB = 128;                          // W tile: [channel group of 8][k4][8 channels][16 B]
 constexpr uint32_t idesc_tf32(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kM >> 4) << 24); }
 constexpr uint32_t kSpinLimit = 1u << 27;
@@ -451,6 +452,8 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
   uint64_t *full = bars, *empty = bars + kStagesTc, *tfull = bars + 2 * kStagesTc, *tempty = bars + 2 * kStagesTc + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStagesTc + 4);
   float* s_bias = reinterpret_cast<float*>(tmem_slot + 1);        // 32 floats, zero padded
+  uint64_t* raw_bar = bars + 32;                                  // [kGroups][kRawDepth]
+  unsigned char* sRaw = sW + 2 * wbytes + 512;                    // [kGroups][kRawDepth][32 rows][128 px] fp32
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int HW = H * W, nks = Cin / kKs;
   const uint32_t sboB = (uint32_t)(Cin / 4) * 128;
@@ -458,6 +461,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
   if (tid == 0) {
     for (int s = 0; s < kStagesTc; ++s) { mbar_init(full + s, 4); mbar_init(empty + s, 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }
+    for (int i = 0; i < kGroups * kRawDepth; ++i) mbar_init(raw_bar + i, 128);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kMmaWarp) {
@@ -484,27 +488,44 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
     // thread = pixel px = TMEM lane (warp & 3 is the lane quarter a warp may touch, and groups start at multiples of 4)
     const int grp = warp >> 2, px = tid & (kM - 1);
     const int total = my_tiles * nks;
-    int l_j = grp;                                  // stage index of the load stream (tile-major, then channel block)
-    auto load = [&](float (&v)[kKs]) {
-      if (l_j >= total) return;
-      const int t = l_j / nks, ks = l_j - t * nks;
-      const int tile = blockIdx.x + t * gridDim.x;
-      const int bv = tile / tiles_per_img, p = (tile - bv * tiles_per_img) * kM + px;
-      if (p < HW) {
-        const float* src = X + ((size_t)bv * Cin + ks * kKs) * HW + p;
-#pragma unroll
-        for (int i = 0; i < kKs; ++i) v[i] = __ldg(src + (size_t)i * HW);   // ld.cg / .cs / .lu variants: 146-149 us, no difference (measured)
-      } else {
-#pragma unroll
-        for (int i = 0; i < kKs; ++i) v[i] = 0.f;
-      }
-      l_j += kGroups;
-    };
-    int s_j = grp;                                  // stage index of the store stream
     const uint32_t lane_base = tmem_base + kRingCol0 + ((uint32_t)((warp & 3) * 32) << 16);
-    auto store = [&](const float (&v)[kKs]) {
-      const int slot = s_j % kStagesTc;
-      mbar_wait(empty + slot, ((s_j / kStagesTc) & 1) ^ 1);   // the MMAs that read this slot have completed
+    // Raw ring, private to the group: kRawDepth of ITS stages in flight as 16-byte cp.async (lanes along the 512-byte pixel
+    // run of a channel row), each thread posting a no-increment arrive that fires when its copies have landed. Registers
+    // hold one stage only; the depth of the prefetch no longer depends on them (the register-prefetch version was bound by
+    // the latency of its loads at 148 us).
+    float* const raw_g = reinterpret_cast<float*>(sRaw) + grp * kRawDepth * (kKs * kM);
+    uint64_t* const raw_full = raw_bar + grp * kRawDepth;
+    const int t128 = tid & 127;
+    auto issue = [&](int n) {                       // n-th own stage of this group = global stage grp + n * kGroups
+      const int j = grp + n * kGroups;
+      if (j >= total) return;
+      const int t = j / nks, ks = j - t * nks;
+      const int tile = blockIdx.x + t * gridDim.x;
+      const int bv = tile / tiles_per_img, p0 = (tile - bv * tiles_per_img) * kM;
+      float* dst = raw_g + (n % kRawDepth) * (kKs * kM);
+      const float* src = X + ((size_t)bv * Cin + ks * kKs) * HW + p0;
+#pragma unroll
+      for (int i = 0; i < kKs * kM / 4 / 128; ++i) {
+        const int idx = t128 + 128 * i, row = idx >> 5, c4 = (idx & 31) * 4;
+        const bool ok = p0 + c4 < HW;               // H*W % 4 == 0 (usable): a 16-byte piece is all in or all out
+        cp_async16(dst + row * kM + c4, ok ? src + (size_t)row * HW + c4 : X, ok);
+      }
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(raw_full + n % kRawDepth)) : "memory");
+    };
+#pragma unroll
+    for (int n = 0; n < kRawDepth; ++n) issue(n);
+    int n = 0;
+    for (int j = grp; j < total; j += kGroups, ++n) {
+      const int rs = n % kRawDepth;
+      mbar_wait(raw_full + rs, (n / kRawDepth) & 1);
+      float v[kKs];
+      const float* rp = raw_g + rs * (kKs * kM) + px;
+#pragma unroll
+      for (int i = 0; i < kKs; ++i) v[i] = rp[i * kM];          // lanes = consecutive pixels: conflict free
+      asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");   // the group has read the slot: refill it
+      issue(n + kRawDepth);
+      const int slot = j % kStagesTc;
+      mbar_wait(empty + slot, ((j / kStagesTc) & 1) ^ 1);   // the MMAs that read this TMEM slot have completed
       tc_fence_after();
       const uint32_t t0 = lane_base + slot * kStageCols;
 #pragma unroll
@@ -522,14 +543,6 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(full + slot);
-      s_j += kGroups;
-    };
-    float b0[kKs], b1[kKs];
-    load(b0);
-    load(b1);
-    for (int j = grp; j < total; j += 2 * kGroups) {   // a buffer is refilled right after it is stored: both stay in flight
-      store(b0); load(b0);
-      if (j + kGroups < total) { store(b1); load(b1); }
     }
   } else if (warp == kMmaWarp) {
     // The whole warp walks the loop with warp-uniform values (TMEM base re-broadcast with a shuffle so that the compiler
@@ -1000,8 +1013,8 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
 inline size_t bw_smem_bytes() { return (size_t)kBwRawStages * kBwRawBytes + kBwSlots * kBwBTile + 512; }
 inline bool bw_usable(int Cin, int Cout, int HW) { return Cout <= kN && (Cin == 128 || Cin == 256) && HW % kBwPx == 0; }
 
-inline size_t smem_bytes(int Cin) { return 2 * (size_t)kN * Cin * 4 + 512; }
-inline bool usable(int Cin, int Cout) { return Cout <= kN && Cin % kKs == 0 && Cin >= kKs && Cin <= 512; }
+inline size_t smem_bytes(int Cin) { return 2 * (size_t)kN * Cin * 4 + 512 + (size_t)kGroups * kRawDepth * kKs * kM * 4; }
+inline bool usable(int Cin, int Cout, int HW) { return Cout <= kN && Cin % kKs == 0 && Cin >= kKs && Cin <= 256 && HW % 4 == 0; }
 }  // namespace tc
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -1035,7 +1048,7 @@ size_t pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W) {
 cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* bias, float* out_hwcp, void* ws,
                               int BV, int Cin, int Cout, int H, int W, cudaStream_t st) {
   const int Cp = padded_channels(Cout), HW = H * W;
-  if (tc::usable(Cin, Cout) && !force_ffma()) {
+  if (tc::usable(Cin, Cout, HW) && aligned16(x) && !force_ffma()) {
     k_pw_zero_border<<<BV, 256, 0, st>>>(out_hwcp, Cp, H, W);
     const int tiles_per_img = (HW + tc::kM - 1) / tc::kM, ntiles = BV * tiles_per_img;
     const int smem = (int)tc::smem_bytes(Cin);

@@ -84,3 +84,49 @@ def test_algebraic_tail_is_capturable():
     step()
     torch.cuda.synchronize()
     assert torch.equal(got["X"], out["X"]) and torch.equal(got["g"], out["g"])
+
+
+def test_process_features_into_unproject_is_capturable():
+    """K7 -> .view -> K1 (no layout pass in either direction) recorded once, replayed on new backbone features: the tcgen05
+    kernels (256 -> 32 channels) launch on the capturing stream, and the gather-layout registry keys on storage addresses,
+    which a graph's private pool keeps stable."""
+    B, V, N = 2, 4, 12
+    d = synthetic.make_unproject_inputs(B=B, V=V, C=32, H=32, W=32, N=N, seed=4, train=True)
+    proj, coord = d["proj_matricies"].cuda(), d["coord_volumes"].cuda()
+    gen = torch.Generator().manual_seed(9)
+    xs = [torch.randn(B * V, 256, 32, 32, generator=gen).cuda() for _ in range(2)]
+    static_x = xs[0].clone()
+    net = lt_b200.ProcessFeatures().cuda()
+    gvol = torch.randn(B, 32, N, N, N, device="cuda")
+    out = {}
+
+    def step():
+        x = static_x.detach().requires_grad_(True)
+        for p in net.parameters():
+            p.grad = None
+        f = net(x)
+        f = f.view(B, V, *f.shape[1:])
+        vol = lt_b200.unproject_heatmaps(f, proj, coord, "softmax")
+        vol.backward(gvol)
+        out.update(vol=vol.detach(), gx=x.grad, gw=net[0].weight.grad, gb=net[0].bias.grad)
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        step()
+    captured = dict(out)
+    for i in (1, 0):
+        static_x.copy_(xs[i])
+        graph.replay()
+        torch.cuda.synchronize()
+        got = {k: v.clone() for k, v in captured.items()}
+        step()
+        torch.cuda.synchronize()
+        assert torch.equal(got["vol"], out["vol"])
+        for k in ("gx", "gw", "gb"):      # downstream of K1's atomically ordered scatter
+            assert (got[k] - out[k]).abs().max().item() <= 1e-4 * out[k].abs().max().item(), k
