@@ -42,6 +42,14 @@ SHAPES = [  # BV, Cin, Cout, H, W, bias
     (2, 16, 130, 6, 6, True),       # Cp = 256
     (1, 3, 1, 1, 1, True),          # a single pixel
     (5, 256, 32, 19, 23, True),     # pixel tile tail
+    # dispatch corners of the tcgen05 kernels (forward: Cout <= 32, Cin % 32 == 0, Cin <= 256, H*W % 4 == 0; backward-data:
+    # Cin % 64 == 0; backward-weight: Cin in {128, 256}, H*W % 32 == 0)
+    (3, 128, 32, 16, 16, True),     # one 128-channel block in the weight gradient, N = 128 accumulator in backward-data
+    (2, 64, 20, 8, 8, True),        # Cin = 64: tensor-core forward and backward-data, FFMA weight gradient; zero-padded Cout
+    (1, 256, 7, 12, 12, False),     # H*W = 144: partial 128-pixel tile on the tensor cores, not a multiple of 32 -> FFMA dW
+    (70, 256, 32, 8, 8, True),      # more maps than tiles per map: every CTA walks several maps, half-empty tiles
+    (2, 256, 32, 40, 48, True),     # 15 tiles per map (H*W = 1920), more tiles than CTAs would get in one wave at B*V = 64
+    (1, 32, 32, 4, 8, True),        # one 32-channel stage, a single 32-pixel chunk
 ]
 
 
@@ -230,3 +238,21 @@ def test_drop_in_module_keeps_state_dict():
         assert rel_err(net.process_features(x).cpu(), want.cpu()) < 1e-5
     finally:
         torch.backends.cudnn.allow_tf32 = saved
+
+
+def _fuzz_cases(n=14, seed=20261105):
+    import random
+    rnd = random.Random(seed)
+    cases = []
+    for _ in range(n):
+        cin = rnd.choice([32, 64, 96, 128, 192, 256, 256, 256, 24, 300])
+        cout = rnd.choice([32, 32, 17, 8, 33])
+        h, w = rnd.randint(1, 20), rnd.choice([4, 8, 12, 16, 5, 9])
+        cases.append((rnd.randint(1, 5), cin, cout, h, w, rnd.random() < 0.7))
+    return cases
+
+
+@pytest.mark.parametrize("BV,Cin,Cout,H,W,with_bias", _fuzz_cases())
+def test_random_shapes_over_the_dispatch_space(BV, Cin, Cout, H, W, with_bias):
+    """Seeded random shapes across the tensor-core / FFMA dispatch boundaries of all three kernels."""
+    test_oracle_shapes(BV, Cin, Cout, H, W, with_bias)
