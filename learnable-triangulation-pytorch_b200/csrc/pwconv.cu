@@ -816,8 +816,10 @@ inline bool bd_usable(int Cin, int Cout) { return Cout <= kN && Cin % 64 == 0 &&
 constexpr int kBwPx = 32, kBwRawStages = 4, kBwSlots = 2, kBwConvWarps = 8, kBwMmaWarp = 8, kBwWarps = 9;
 constexpr uint32_t kBwRowPitch = 144;                                   // raw X row: 128 B + 16 B pad
 constexpr uint32_t kBwRawX = 256 * kBwRowPitch, kBwRawBytes = kBwRawX + kBwPx * 128;   // 36,864 + 4,096
-constexpr uint32_t kBwBTile = 2 * kN * kBwPx * 4;                        // 8 KB: 64 rows x 32 pixels
-constexpr uint32_t kBwLboB = 128, kBwSboB = (kBwPx / 4) * 128;           // [channel group of 8][p4][8 channels][16 B]
+// B tile [channel group of 8][p4][8 channels][16 B]: 64 rows x 32 pixels; 16 bytes of padding per channel group make the
+// transposing 4-byte stores of a warp (8 channel quads x 4 pixels) hit 32 different banks (unpadded: 4-way conflicts)
+constexpr uint32_t kBwLboB = 128, kBwSboB = (kBwPx / 4) * 128 + 16;
+constexpr uint32_t kBwBTile = (2 * kN / 8) * kBwSboB;
 constexpr uint32_t kBwAccCols = 3 * kN, kBwRing0 = 2 * kBwAccCols, kBwSlotCols = 2 * 2 * kBwPx;
 
 __global__ void __launch_bounds__(kBwWarps * 32, 1)

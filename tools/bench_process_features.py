@@ -1,8 +1,7 @@
 #!/usr/bin/env python
 """Measurement of K7 (process_features 1x1 convolution written in the gather layout) at BASELINE
 config 3's shape: B*V = 64 maps, 256 -> 32 channels, 96 x 96. Each kernel through the C ABI with CUDA events on the
-launching stream, next to the reference's statement (F.conv2d, the oracle restatement with CUDA tensors — tools/ may
-use it as the baseline, the product never does) with TF32 off (the fp32 result the parity bar is) and on (cuDNN's
+launching stream, next to the reference's statement (`nn.Conv2d(256, 32, 1)` = F.conv2d, stock cuDNN on the same GPU) with TF32 off (the fp32 result the parity bar is) and on (cuDNN's
 default). One JSON line. Inputs (604 MB) exceed L2, so no flush between iterations."""
 import json
 import os
@@ -13,7 +12,6 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import lt_b200  # noqa: E402
-from oracle import ref_ops  # noqa: E402
 
 
 def timed(fn, n=30, warm=5):
@@ -66,11 +64,11 @@ def main():
         torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = tf32
         xr, wr, br = x.clone().requires_grad_(True), w4.clone().requires_grad_(True), b.clone().requires_grad_(True)
         gy = torch.randn(BV, Cout, H, W, device="cuda")
-        f = timed(lambda: ref_ops.process_features(xr, wr, br), n=10, warm=3)
+        f = timed(lambda: torch.nn.functional.conv2d(xr, wr, br), n=10, warm=3)
 
         def fb():
             xr.grad = wr.grad = br.grad = None
-            ref_ops.process_features(xr, wr, br).backward(gy)
+            torch.nn.functional.conv2d(xr, wr, br).backward(gy)
         return f, timed(fb, n=10, warm=3)
     f32 = stock(False)
     tf32 = stock(True)

@@ -16,7 +16,12 @@ for r in rows[2:]:
 if kre:
     args = ["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kre]
     rows = list(csv.reader(subprocess.run(args, capture_output=True, text=True).stdout.splitlines()))
-    hdr = rows[1]; data = rows[2:]
+    hi = [i for i, r in enumerate(rows) if 'Source' in r and 'Instructions Executed' in r][0]
+    hdr = rows[hi]; data = [r for r in rows[hi + 1:] if len(r) == len(hdr) and r[hdr.index('Instructions Executed')].isdigit()]
+    for rep in (4, 2):  # the source page repeats the listing once per captured launch of the kernel
+        n = len(data) // rep
+        if n and len(data) % rep == 0 and [r[hdr.index('Source')] for r in data[:n]] == [r[hdr.index('Source')] for r in data[n:2 * n]]:
+            data = data[:n]; break
     iS = hdr.index('Source'); iE = hdr.index('Instructions Executed')
     tot = sum(int(r[iE]) for r in data); mx = max(int(r[iE]) for r in data)
     nw = int(data[0][iE])
