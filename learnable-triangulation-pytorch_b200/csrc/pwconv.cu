@@ -806,14 +806,15 @@ inline bool bd_usable(int Cin, int Cout) { return Cout <= kN && Cin % 64 == 0 &&
 // channels, K = pixels. A = X rows (pixel-contiguous = K-major as stored), B = the gradient tile transposed to channel rows.
 // Persistent CTAs walk 32-pixel chunks and keep their partial dW in TMEM until the end; the per-CTA partials go to the same
 // workspace as the FFMA kernel's and are merged in CTA order by k_pw_reduce_partials (deterministic).
-//   warps 0-7   fill a 4-deep raw ring with 16-byte cp.async three chunks ahead (completion counted by an mbarrier through
-//               cp.async.mbarrier.arrive.noinc), then act as converters, thread = input channel row = TMEM lane:
+//   warps 0-15  two sets of 256 threads alternating chunks; a set fills its two raw stages with 16-byte cp.async (completion
+//               counted by an mbarrier through cp.async.mbarrier.arrive.noinc), then converts, thread = input channel row = TMEM lane:
 //               8 x LDS.128 of the row (144-byte pitch: conflict free),
 //               split, tcgen05.st of hi and lo into the A ring in tensor memory; the same threads transpose + split the
 //               gradient texels into the UMMA canonical B tile ([G_hi | G_lo] as 64 rows) and keep the bias-gradient sums
-//   warp  8     per 8 pixels and channel block: one N = 64 MMA (X_hi x [G_hi | G_lo]) and one N = 32 (X_lo x G_hi)
+//   warp  16    per 8 pixels and channel block: one N = 64 MMA (X_hi x [G_hi | G_lo]) and one N = 32 (X_lo x G_hi)
 // TMEM map: [0,192) accumulators of the two channel blocks (hi·hi | hi·lo | lo·hi), [192,448) two A slots of 2 x 64 columns.
-constexpr int kBwPx = 32, kBwRawStages = 4, kBwSlots = 2, kBwConvWarps = 8, kBwMmaWarp = 8, kBwWarps = 9;
+constexpr int kBwPx = 32, kBwRawStages = 4, kBwSlots = 2, kBwSetWarps = 8, kBwSets = 2, kBwConvWarps = kBwSets * kBwSetWarps,
+              kBwMmaWarp = kBwConvWarps, kBwWarps = kBwConvWarps + 1;
 constexpr uint32_t kBwRowPitch = 144;                                   // raw X row: 128 B + 16 B pad
 constexpr uint32_t kBwRawX = 256 * kBwRowPitch, kBwRawBytes = kBwRawX + kBwPx * 128;   // 36,864 + 4,096
 // B tile [channel group of 8][p4][8 channels][16 B]: 64 rows x 32 pixels; 16 bytes of padding per channel group make the
@@ -830,8 +831,7 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
   unsigned char* sRaw = sm;                                              // [kBwRawStages][X rows | G texels]
   unsigned char* sB = sm + kBwRawStages * kBwRawBytes;                   // [kBwSlots][8 KB]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sB + kBwSlots * kBwBTile);
-  uint64_t *full_raw = bars, *empty_raw = bars + kBwRawStages, *full_mma = bars + 2 * kBwRawStages,
-           *empty_mma = full_mma + kBwSlots, *done = empty_mma + kBwSlots;
+  uint64_t *full_raw = bars, *full_mma = bars + kBwRawStages, *empty_mma = full_mma + kBwSlots, *done = empty_mma + kBwSlots;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
   float* s_db = reinterpret_cast<float*>(tmem_slot + 1);                 // 32 floats
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -839,8 +839,8 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
   const int nblk = Cin / kM;                                            // 1 or 2 channel blocks
 
   if (tid == 0) {
-    for (int s = 0; s < kBwRawStages; ++s) { mbar_init(full_raw + s, kBwConvWarps * 32); mbar_init(empty_raw + s, kBwConvWarps); }
-    for (int s = 0; s < kBwSlots; ++s) { mbar_init(full_mma + s, kBwConvWarps); mbar_init(empty_mma + s, 1); }
+    for (int s = 0; s < kBwRawStages; ++s) mbar_init(full_raw + s, kBwSetWarps * 32);
+    for (int s = 0; s < kBwSlots; ++s) { mbar_init(full_mma + s, kBwSetWarps); mbar_init(empty_mma + s, 1); }
     mbar_init(done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -882,11 +882,15 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
       __syncwarp();
     }
   } else {
-    // converters: thread = input channel row `tid` (< Cin) = TMEM lane tid & 127 of channel block tid >> 7
-    const int mb = tid >> 7;
-    const bool row_ok = tid < Cin;
+    // Two converter sets of 256 threads alternate chunks (set s: chunks i = s, s+2, ...; raw stages s and s+2, A slot and B
+    // tile s): the wait -> LDS -> split -> tcgen05.st -> fence -> arrive chain of one chunk takes about one chunk time at
+    // HBM speed, so a single set bounded the kernel at 139 us (measured).
+    // thread = input channel row `ct` (< Cin) = TMEM lane ct & 127 of channel block ct >> 7
+    const int set = warp / kBwSetWarps, ct = tid & (kBwSetWarps * 32 - 1);
+    const int mb = ct >> 7;
+    const bool row_ok = ct < Cin;
     const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + kBwRing0 + mb * 2 * kBwPx;
-    const int gp = tid >> 3, gc4 = tid & 7;           // gradient texel duty: pixel gp, channels 4*gc4..+3
+    const int gp = ct >> 3, gc4 = ct & 7;           // gradient texel duty: pixel gp, channels 4*gc4..+3
     float bacc[4] = {0.f, 0.f, 0.f, 0.f};
     // raw ring fill: 16-byte cp.async, lanes along the pixels of a row (a warp instruction = four whole 128-byte lines);
     // each thread posts a no-increment arrive on the stage's mbarrier that fires when ITS copies have landed. (One warp
@@ -894,33 +898,31 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
     auto issue = [&](int i) {
       if (i >= my_chunks) return;
       const int s = i % kBwRawStages;
-      mbar_wait(empty_raw + s, ((i / kBwRawStages) & 1) ^ 1);
       const int chunk = blockIdx.x + i * gridDim.x;
       const int bv = chunk / chunks_per_img, p0 = (chunk - bv * chunks_per_img) * kBwPx;
       float* raw = reinterpret_cast<float*>(sRaw + s * kBwRawBytes);
-      const float* xs = X + ((size_t)bv * Cin + (tid >> 3)) * HW + p0 + (tid & 7) * 4;
+      const float* xs = X + ((size_t)bv * Cin + (ct >> 3)) * HW + p0 + (ct & 7) * 4;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const int row = (tid >> 3) + 32 * j;
-        if (row < Cin) cp_async16(raw + row * (kBwRowPitch / 4) + (tid & 7) * 4, xs + (size_t)(32 * j) * HW, true);
+        const int row = (ct >> 3) + 32 * j;
+        if (row < Cin) cp_async16(raw + row * (kBwRowPitch / 4) + (ct & 7) * 4, xs + (size_t)(32 * j) * HW, true);
       }
       const int p = p0 + gp, y = p / W, x = p - y * W;   // HW % 32 == 0: every pixel of the chunk exists
       cp_async16(raw + kBwRawX / 4 + gp * 32 + gc4 * 4, G + (((size_t)bv * Hp + y + 1) * Wp + x + 1) * Cp + gc4 * 4, true);
       asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(full_raw + s)) : "memory");
     };
-    issue(0); issue(1); issue(2);
-    for (int i = 0; i < my_chunks; ++i) {
-      const int s = i % kBwRawStages, slot = i % kBwSlots;
-      issue(i + kBwRawStages - 1);
+    issue(set); issue(set + kBwSets);
+    for (int i = set; i < my_chunks; i += kBwSets) {
+      const int s = i % kBwRawStages, slot = i % kBwSlots;   // slot == set
       mbar_wait(full_raw + s, (i / kBwRawStages) & 1);
       const unsigned char* raw = sRaw + s * kBwRawBytes;
       float4 xr[kBwPx / 4];
 #pragma unroll
       for (int q = 0; q < kBwPx / 4; ++q)
-        xr[q] = row_ok ? *reinterpret_cast<const float4*>(raw + tid * kBwRowPitch + q * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+        xr[q] = row_ok ? *reinterpret_cast<const float4*>(raw + ct * kBwRowPitch + q * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
       const float4 g = *reinterpret_cast<const float4*>(raw + kBwRawX + gp * 128 + gc4 * 16);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(empty_raw + s);      // raw stage consumed (values are in registers)
+      asm volatile("bar.sync %0, 256;" ::"r"(1 + set) : "memory");   // the set has the raw stage in registers: refill it
+      issue(i + kBwRawStages);
       mbar_wait(empty_mma + slot, ((i / kBwSlots) & 1) ^ 1);
       tc_fence_after();
       const uint32_t t0 = lane_base + slot * kBwSlotCols;
@@ -956,13 +958,13 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
       if (lane == 0) mbar_arrive(full_mma + slot);
     }
     // epilogue: this thread's dW row (input channel tid, all 32 output channels) from the three partial accumulators
-    if (my_chunks > 0) {
+    if (my_chunks > 0 && set == 0) {
       mbar_wait(done, 0);
       tc_fence_after();
     }
-    if (row_ok) {
+    if (row_ok && set == 0) {
       const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + mb * kBwAccCols;
-      float* dst = part_w + ((size_t)blockIdx.x * CinPad + tid) * Cp;
+      float* dst = part_w + ((size_t)blockIdx.x * CinPad + ct) * Cp;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         float acc[16];
@@ -995,13 +997,13 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
       v += __shfl_xor_sync(0xffffffffu, v, 16);
       bacc[j] = v;
     }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync 3, 512;" ::: "memory");
     for (int w = 0; w < kBwConvWarps; ++w) {          // warps add in warp order: deterministic
       if (warp == w && lane < 8) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) s_db[lane * 4 + j] += bacc[j];
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 3, 512;" ::: "memory");
     }
     if (tid < kN) part_b[(size_t)blockIdx.x * Cp + tid] = s_db[tid];
   }
