@@ -120,3 +120,42 @@ def test_coord_volume_specs_round_like_the_reference():
     assert np.isclose(R[0, 0], np.cos(0.3), atol=1e-7)
     with pytest.raises(RuntimeError):
         volumetric.build_coord_volumes(base, 2500.0, 8, device="cpu")
+
+
+def test_use_fused_process_features_keeps_parameters_and_state_dict():
+    """Host side of K7's drop-in (no GPU needed): the module of an existing net is switched in place, parameters, their
+    identity and the state_dict keys of the reference (`process_features.0.weight/.bias`) are unchanged; anything that is
+    not `nn.Sequential(nn.Conv2d(cin, cout, 1))` is refused; CPU tensors fail loudly (no fallback)."""
+    import torch
+    from torch import nn
+
+    import lt_b200
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.process_features = nn.Sequential(nn.Conv2d(256, 32, 1))   # mvn/models/triangulation.py:238-240
+
+    net = Net()
+    before = {k: v.clone() for k, v in net.state_dict().items()}
+    wid = id(net.process_features[0].weight)
+    assert lt_b200.use_fused_process_features(net) is net
+    assert isinstance(net.process_features, lt_b200.ProcessFeatures)
+    assert list(net.state_dict()) == ["process_features.0.weight", "process_features.0.bias"]
+    assert id(net.process_features[0].weight) == wid
+    for k, v in net.state_dict().items():
+        assert torch.equal(v, before[k])
+    fresh = Net()
+    fresh.load_state_dict(net.state_dict())                              # checkpoints travel both ways
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        net.process_features(torch.zeros(1, 256, 4, 4))
+
+    class Other(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.process_features = nn.Sequential(nn.Conv2d(256, 32, 3, padding=1))
+
+    with pytest.raises(TypeError):
+        lt_b200.use_fused_process_features(Other())
+    with pytest.raises(RuntimeError):
+        lt_b200.process_features(torch.zeros(1, 8, 4, 4), torch.zeros(4, 8, 3, 3))
