@@ -159,3 +159,56 @@ def test_use_fused_process_features_keeps_parameters_and_state_dict():
         lt_b200.use_fused_process_features(Other())
     with pytest.raises(RuntimeError):
         lt_b200.process_features(torch.zeros(1, 8, 4, 4), torch.zeros(4, 8, 3, 3))
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/mvn"), reason="the reference tree only exists in the build container")
+def test_reference_net_forward_reaches_the_drop_ins_at_its_own_call_sites():
+    """Wiring evidence for SURVEY 8(f) row 4 with the UNMODIFIED reference `VolumetricTriangulationNet.forward`: built here on
+    the CPU (ResNet-18 backbone, random weights, a two-view 64 x 64 batch with real `multiview.Camera` objects), patched,
+    and run. There is no GPU in this container and no CPU fallback in the product, so the forward must die with the
+    product's own error, raised from the reference's own call site: `self.process_features(features)` (triangulation.py:345)
+    once `use_fused_process_features` has switched the module, `op.unproject_heatmaps(...)` (:349) with the ops patched only.
+    (On the GPU box the reference does not exist; the numerics of the same chain are covered by tests/test_gpu_pipeline.py and
+    tests/test_gpu_process_features.py::test_chain_into_unproject.)"""
+    import traceback
+    from types import SimpleNamespace as NS
+
+    import numpy as np
+
+    sys.path.insert(0, "/root/reference")
+    try:
+        from mvn.models.triangulation import VolumetricTriangulationNet
+        from mvn.utils.multiview import Camera
+        cfg = NS(model=NS(backbone=NS(num_joints=17, num_layers=18, style="simple", init_weights=False, checkpoint=None,
+                                      alg_confidences=False, vol_confidences=False),
+                          volume_aggregation_method="softmax", volume_softmax=True, volume_multiplier=1.0, volume_size=8,
+                          cuboid_side=2500.0, kind="mpii", use_gt_pelvis=False, heatmap_softmax=True,
+                          heatmap_multiplier=100.0))
+        torch.manual_seed(0)
+        net = VolumetricTriangulationNet(cfg, device="cpu").eval()
+        K = np.array([[1145.0, 0, 32.0], [0, 1145.0, 32.0], [0, 0, 1.0]])
+        cams = [[Camera(np.eye(3), np.array([[0.0], [0.0], [5000.0 + 100 * v]]), K)] for v in range(2)]
+        batch = {"cameras": cams, "pred_keypoints_3d": np.zeros((1, 17, 3))}
+        images = torch.randn(1, 2, 3, 64, 64)
+
+        def failing_site():
+            with pytest.raises(RuntimeError, match="no CPU fallback") as ei:
+                with torch.no_grad():
+                    net(images, None, batch)
+            frames = traceback.extract_tb(ei.tb)
+            ref = [f for f in frames if f.filename.endswith("mvn/models/triangulation.py")]
+            ours = [f for f in frames if "learnable-triangulation-pytorch_b200" in f.filename]
+            assert ref and ours
+            return ref[-1].line, os.path.basename(ours[0].filename)
+
+        lt_b200.patch_reference()
+        try:
+            line, mod = failing_site()
+            assert "op.unproject_heatmaps(" in line and mod == "op.py"
+            lt_b200.use_fused_process_features(net)
+            line, mod = failing_site()
+            assert "self.process_features(features)" in line and mod == "triangulation.py"
+        finally:
+            lt_b200.unpatch_reference()
+    finally:
+        sys.path.remove("/root/reference")
