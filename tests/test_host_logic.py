@@ -208,6 +208,12 @@ def test_reference_net_forward_reaches_the_drop_ins_at_its_own_call_sites():
             lt_b200.use_fused_process_features(net)
             line, mod = failing_site()
             assert "self.process_features(features)" in line and mod == "triangulation.py"
+            # the algebraic net: first drop-in on its path is the 2-D soft-argmax (triangulation.py:164)
+            from mvn.models.triangulation import AlgebraicTriangulationNet
+            cfg.model.use_confidences = False   # the confidence head pools 64 x 64 inputs away
+            net = AlgebraicTriangulationNet(cfg, device="cpu").eval()
+            line, mod = failing_site()
+            assert "op.integrate_tensor_2d(" in line and mod == "op.py"
         finally:
             lt_b200.unpatch_reference()
     finally:
