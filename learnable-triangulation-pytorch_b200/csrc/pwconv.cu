@@ -1022,6 +1022,7 @@ inline bool usable(int Cin, int Cout, int HW) { return Cout <= kN && Cin % kKs =
 }  // namespace tc
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+inline bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 constexpr int kFwdSmem = kStages * (kKc * kPx + kKc * kCo) * 4;      // 73,728 B -> 3 CTAs per SM
 constexpr int kBwdDataSmem = (kCo * kPx + kCo * kKn) * 4;            // 65,536 B -> 3 CTAs per SM
 constexpr int kBwdWeightSmem = kWgStages * kWgStageFloats * 4;       // 90,112 B -> 2 CTAs per SM
@@ -1052,7 +1053,7 @@ size_t pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W) {
 cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* bias, float* out_hwcp, void* ws,
                               int BV, int Cin, int Cout, int H, int W, cudaStream_t st) {
   const int Cp = padded_channels(Cout), HW = H * W;
-  if (tc::usable(Cin, Cout, HW) && aligned16(x) && !force_ffma()) {
+  if (tc::usable(Cin, Cout, HW) && aligned16(x) && aligned32(out_hwcp) && !force_ffma()) {   // epilogue: 32-byte stores
     k_pw_zero_border<<<BV, 256, 0, st>>>(out_hwcp, Cp, H, W);
     const int tiles_per_img = (HW + tc::kM - 1) / tc::kM, ntiles = BV * tiles_per_img;
     const int smem = (int)tc::smem_bytes(Cin);

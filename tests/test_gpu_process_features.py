@@ -214,6 +214,30 @@ def test_guard_bands_and_empty_batch():
     assert L.lt_pwconv_fwd(None, None, None, None, None, 1, 0, 32, 8, 8, None) == -1
 
 
+def test_forward_with_a_16_byte_aligned_output_buffer():
+    """The tensor-core forward stores 32 bytes per instruction; an output buffer that is only 16-byte aligned (legal per
+    include/lt_b200.h) must take the other kernel and give the same values."""
+    L = _lib.lib()
+    BV, Cin, Cout, H, W = 2, 256, 32, 16, 16
+    gen = torch.Generator().manual_seed(31)
+    x = torch.randn(BV, Cin, H, W, generator=gen).cuda()
+    w = (torch.randn(Cout, Cin, generator=gen) / 16).cuda()
+    b = torch.randn(Cout, generator=gen).cuda()
+    n = L.lt_feat_layout_elems(BV, Cout, H, W)
+    ws = torch.empty(max(L.lt_pwconv_ws_bytes(BV, Cin, Cout, H, W), 4) // 4, device="cuda")
+    buf = torch.zeros(n + 16, device="cuda")
+    outs = []
+    for shift in (0, 4):                        # 0: 32-byte aligned (tcgen05 path), 4 floats: 16-byte aligned only
+        out = buf[shift:shift + n]
+        assert out.data_ptr() % 32 == (16 if shift else 0)
+        _lib.check(L.lt_pwconv_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), out.data_ptr(), ws.data_ptr(), BV, Cin, Cout,
+                                   H, W, None))
+        torch.cuda.synchronize()
+        outs.append(out.clone())
+    assert rel_err(outs[1].cpu(), outs[0].cpu()) < 2e-6
+    assert outs[0].abs().max() > 0
+
+
 def test_drop_in_module_keeps_state_dict():
     torch.manual_seed(0)
     ref = torch.nn.Sequential(torch.nn.Conv2d(256, 32, 1)).cuda()          # triangulation.py:238-240
