@@ -168,7 +168,10 @@ int lt_softargmax_bwd_add_sparse(const float *prob, const int *idx, const float 
  * Backward: grad_hwcp is the gradient map lt_unproject_bwd scatters into (same layout; border and padded channels are
  * ignored).  grad_x (BV, Cin, H, W) fully overwritten; grad_weight (Cout, Cin) and grad_bias (Cout, may be NULL) fully
  * overwritten, summed in a fixed order (deterministic).  ws: lt_pwconv_ws_bytes() bytes of scratch, 16-byte aligned
- * (forward and backward-weight; may be shared, contents are not kept between calls). */
+ * (forward and backward-weight; may be shared, contents are not kept between calls).
+ * At the reference's shape (Cout <= 32, Cin = 128 or 256, H*W a multiple of 32, x 16-byte and out_hwcp 32-byte aligned)
+ * all three run on the tcgen05 tensor cores with a three-product TF32 split (fp32 accuracy); other shapes and alignments
+ * run fp32 FMA kernels with the same results to 2e-6. */
 size_t lt_pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W);
 int lt_pwconv_fwd(const float *x, const float *weight, const float *bias, float *out_hwcp, void *ws,
                   int BV, int Cin, int Cout, int H, int W, void *stream);
