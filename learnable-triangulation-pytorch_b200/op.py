@@ -114,7 +114,9 @@ class _Unproject(torch.autograd.Function):
             out = torch.empty((B, C, N0, N1, N2), device=feat.device, dtype=torch.float32)
             _lib.check(L.lt_unproject_fwd(_lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c), _lib.ptr(conf_c),
                                           _lib.ptr(out), B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
-        ctx.save_for_backward(feat, proj_c, coord_c, conf_c)
+        # with features that already are the gather layout `feat` aliases the caller's tensor: save that tensor as well so
+        # that autograd's version check catches an in-place edit between forward and backward, as it would in the reference
+        ctx.save_for_backward(feat, proj_c, coord_c, conf_c, heatmaps if from_hwcp else None)
         ctx.meta = (B, V, C, H, W, N0, N1, N2, agg, align_corners, heatmaps.dtype,
                     conf.dtype if conf is not None else None, from_hwcp)
         return out
@@ -123,7 +125,7 @@ class _Unproject(torch.autograd.Function):
     @torch.autograd.function.once_differentiable
     def backward(ctx, grad_out):
         L = _lib.lib()
-        feat, proj_c, coord_c, conf_c = ctx.saved_tensors
+        feat, proj_c, coord_c, conf_c, _ = ctx.saved_tensors
         B, V, C, H, W, N0, N1, N2, agg, align_corners, hm_dtype, conf_dtype, from_hwcp = ctx.meta
         need_hm, need_conf = ctx.needs_input_grad[0], ctx.needs_input_grad[3] and conf_c is not None
         g_hm = g_conf = None

@@ -280,3 +280,19 @@ def _fuzz_cases(n=14, seed=20261105):
 def test_random_shapes_over_the_dispatch_space(BV, Cin, Cout, H, W, with_bias):
     """Seeded random shapes across the tensor-core / FFMA dispatch boundaries of all three kernels."""
     test_oracle_shapes(BV, Cin, Cout, H, W, with_bias)
+
+
+def test_in_place_edit_of_the_features_is_caught_like_in_the_reference():
+    """unproject_heatmaps reads the gather-layout buffer behind the features in place; editing them between forward and
+    backward must raise autograd's version error (as it does for the reference's grid_sample), not change the gradient."""
+    B, V, N = 1, 2, 8
+    d = synthetic.make_unproject_inputs(B=B, V=V, C=32, H=16, W=16, N=N, seed=2, train=True)
+    x = torch.randn(B * V, 64, 16, 16, device="cuda", requires_grad=True)
+    w = torch.randn(32, 64, 1, 1, device="cuda", requires_grad=True)
+    f = lt_b200.process_features(x, w, None)
+    f5 = f.view(B, V, *f.shape[1:])
+    vol = lt_b200.unproject_heatmaps(f5, d["proj_matricies"].cuda(), d["coord_volumes"].cuda(), "softmax")
+    with pytest.raises(RuntimeError, match="(?i)inplace"):   # at the edit itself or at backward, depending on the torch version
+        with torch.no_grad():
+            f5.mul_(2.0)
+        vol.sum().backward()
