@@ -632,11 +632,11 @@ __global__ void __launch_bounds__(kWarps * 32, 1)
 // 3xTF32 split; here the accumulator is the big thing (128 x 256 fp32 = 256 TMEM columns, double buffered = all 512), so
 // the small A operand (the pixel tile of the hwcp gradient map, already K-major: 128 contiguous bytes per pixel) goes
 // through shared memory as UMMA canonical tiles and W^T (hi and lo, 64 KB) stays resident.
-//   warps 0-7   two producer groups (thread = pixel) alternating tiles: 8 x LDG.128 of the pixel's texel, split, STS
-//   warp  8     12 tcgen05.mma (N = Cin, K = 8) per tile into one accumulator: lo·hi, hi·lo, hi·hi
-//   warps 9-16  epilogue: a thread owns a pixel and half of the input channels; tcgen05.ld, then one coalesced 128-byte
-//               store per channel and warp into the channel-planar gradient.
-constexpr int kBdStages = 3, kBdProducerWarps = 8, kBdMmaWarp = 8, kBdWarps = 17;
+//   warps 0-3   producers (thread = pixel): 8 x LDG.128 of the pixel's texel one tile ahead, split, STS
+//   warp  4     12 tcgen05.mma (N = Cin, K = 8) per tile into one accumulator: lo·hi, hi·lo, hi·hi
+//   warps 5-20  two epilogue sets alternating tiles: a thread owns a pixel and half of the input channels; tcgen05.ld, then
+//               one coalesced 128-byte store per channel and warp into the channel-planar gradient.
+constexpr int kBdStages = 3, kBdProducerWarps = 4, kBdMmaWarp = 4, kBdEpiSets = 2, kBdWarps = 5 + 8 * kBdEpiSets;
 constexpr uint32_t kBdLboA = (kM / 8) * 128, kBdSboA = 128, kBdTile = kM * kN * 4;   // A: [c4][pixel group][8 px][16 B]
 constexpr uint32_t kBdLboB = 128, kBdSboB = (kN / 4) * 128;                          // W^T: [k group of 8][c4][8 k][16 B]
 
@@ -694,7 +694,7 @@ __global__ void __launch_bounds__(kBdWarps * 32, 1)
   const int my_tiles = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
   if (warp < kBdProducerWarps) {
-    const int grp = warp >> 2, px = tid & (kM - 1);
+    const int px = tid & (kM - 1);
     unsigned char* const base0 = sA + (px >> 3) * kBdSboA + (px & 7) * 16;
     float4 v[kN / 4];
     auto load = [&](int t) {
@@ -711,8 +711,8 @@ __global__ void __launch_bounds__(kBdWarps * 32, 1)
         for (int q = 0; q < kN / 4; ++q) v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
     };
-    load(grp);
-    for (int t = grp; t < my_tiles; t += 2) {
+    load(0);
+    for (int t = 0; t < my_tiles; ++t) {
       const int slot = t % kBdStages;
       mbar_wait(empty + slot, ((t / kBdStages) & 1) ^ 1);
       unsigned char* const base = base0 + slot * 2 * kBdTile;
@@ -729,7 +729,7 @@ __global__ void __launch_bounds__(kBdWarps * 32, 1)
       proxy_fence();
       __syncwarp();
       if (lane == 0) mbar_arrive(full + slot);
-      load(t + 2);
+      load(t + 1);
     }
   } else if (warp == kBdMmaWarp) {
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
@@ -760,10 +760,14 @@ __global__ void __launch_bounds__(kBdWarps * 32, 1)
       __syncwarp();
     }
   } else {
-    const int e = warp - (kBdMmaWarp + 1);            // 0..7
-    const int q = warp & 3, half = e >> 2;            // TMEM lane quarter, and which half of the input channels
+    // Two epilogue sets of eight warps alternate tiles (set s drains accumulator buffer s): the tcgen05.ld phase of one
+    // tile runs under the stores of the other. With one set the two phases added up (4.3 us per tile: 1.5 us without the
+    // stores, 2.8 us of stores at HBM speed; timing experiments in DESIGN.md) and the kernel sat at 135 us.
+    const int e = warp - (kBdMmaWarp + 1);            // 0..15
+    const int set = e >> 3;
+    const int q = warp & 3, half = (e >> 2) & 1;      // TMEM lane quarter, and which half of the input channels
     const int kper = (Cin + 1) / 2;                   // channels [half*kper, min(Cin, (half+1)*kper))
-    for (int t = 0; t < my_tiles; ++t) {
+    for (int t = set; t < my_tiles; t += kBdEpiSets) {
       const int buf = t & 1;
       const int tile = blockIdx.x + t * gridDim.x;
       const int bv = tile / tiles_per_img, p = (tile - bv * tiles_per_img) * kM + q * 32 + lane;
