@@ -7,6 +7,18 @@
 #error "lt_b200 kernels are written for sm_100a (B200) only"
 #endif
 
+// The opt-in above 48 KB of dynamic shared memory is a per-(kernel, device) attribute: smem_opt_in() (layout.cu) issues
+// the driver call the first time a launcher needs `bytes` for `func` on the current device (or needs more than it set
+// before) instead of on every launch, and hands back its error code.
+namespace lt {
+cudaError_t smem_opt_in(const void* func, size_t bytes);
+}
+#define LT_SMEM_OPT_IN_ONCE(KERNEL, BYTES)                                                   \
+  do {                                                                                       \
+    cudaError_t lt_e_ = ::lt::smem_opt_in(reinterpret_cast<const void*>(&KERNEL), (BYTES));  \
+    if (lt_e_ != cudaSuccess) return lt_e_;                                                  \
+  } while (0)
+
 namespace lt {
 
 constexpr int kWarp = 32;

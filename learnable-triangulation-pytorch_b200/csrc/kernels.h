@@ -22,6 +22,12 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
                                  const float* coord, const float* conf, float* grad_feat_hwc,
                                  float* grad_conf, void* conf_ws, const UnprojShape& s, cudaStream_t st);
 
+// on-chip merged formulation of the backward (unproject_bwd_tile.cu); UnprojArgs lives in unproject.cuh
+struct UnprojArgs;
+bool unproject_bwd_tile_eligible(const UnprojShape& s, const float* grad_out);
+size_t unproject_bwd_tile_ws_bytes(const UnprojShape& s);
+cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float* grad_conf, cudaStream_t st);
+
 size_t softargmax_ws_bytes(int B, int J, long long nvox);
 cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,
                                       int J, long long nvox, int softmax, float mult, cudaStream_t st);

@@ -11,6 +11,8 @@
 // (A 16-channel-group variant of this layout, which makes every image row of a group one bulk-copy run for a
 //  shared-memory-staged K1, was measured and set aside: see DESIGN.md "K1 tile experiment".)
 // Pure HBM streaming: algorithmic bytes = BV*H*W*C*4 read + BV*(H+2)*(W+2)*Cp*4 written.
+#include <mutex>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -105,6 +107,27 @@ cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int 
   else
     k_feat_layout<false><<<grid, 256, 0, st>>>(src, dst, C, Cp, H, W, nchunk);
   return cudaGetLastError();
+}
+
+// ---- one-time opt-in for more than 48 KB of dynamic shared memory (see common.cuh) ----
+cudaError_t smem_opt_in(const void* func, size_t bytes) {
+  struct Entry { const void* func; int dev; size_t bytes; };
+  static Entry table[256];
+  static int count = 0;
+  static std::mutex mu;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lock(mu);
+  Entry* hit = nullptr;
+  for (int i = 0; i < count; ++i)
+    if (table[i].func == func && table[i].dev == dev) { hit = &table[i]; break; }
+  if (hit != nullptr && hit->bytes >= bytes) return cudaSuccess;
+  e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) return e;
+  if (hit != nullptr) hit->bytes = bytes;
+  else if (count < 256) table[count++] = Entry{func, dev, bytes};
+  return cudaSuccess;
 }
 
 }  // namespace lt

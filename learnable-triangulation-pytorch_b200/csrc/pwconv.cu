@@ -1061,7 +1061,7 @@ cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* 
     k_pw_zero_border<<<BV, 256, 0, st>>>(out_hwcp, Cp, H, W);
     const int tiles_per_img = (HW + tc::kM - 1) / tc::kM, ntiles = BV * tiles_per_img;
     const int smem = (int)tc::smem_bytes(Cin);
-    cudaError_t e = cudaFuncSetAttribute(tc::k_pwconv_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(&tc::k_pwconv_fwd_tc), (size_t)smem);
     if (e != cudaSuccess) return e;
     tc::k_pwconv_fwd_tc<<<ntiles < 148 ? ntiles : 148, tc::kWarps * 32, smem, st>>>(x, weight, bias, out_hwcp, Cin, Cout,
                                                                                   Cp, H, W, tiles_per_img, ntiles);
@@ -1073,7 +1073,7 @@ cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* 
   dim3 grid((unsigned)((HW + kPx - 1) / kPx), (unsigned)BV, (unsigned)(Cp / kCo));
   const bool vec = (HW % 4 == 0) && aligned16(x);
   auto kern = vec ? k_pwconv_fwd<true> : k_pwconv_fwd<false>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem);
+  cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(kern), (size_t)kFwdSmem);
   if (e != cudaSuccess) return e;
   kern<<<grid, 256, kFwdSmem, st>>>(x, Wt, bias, out_hwcp, Cin, Cout, Cp, H, W);
   return cudaGetLastError();
@@ -1085,7 +1085,7 @@ cudaError_t launch_pwconv_bwd_data(const float* grad_hwcp, const float* weight, 
   if (tc::bd_usable(Cin, Cout) && !force_ffma()) {
     const int tiles_per_img = (HW + tc::kM - 1) / tc::kM, ntiles = BV * tiles_per_img;
     const int smem = (int)tc::bd_smem_bytes(Cin);
-    cudaError_t e = cudaFuncSetAttribute(tc::k_pwconv_bwd_data_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(&tc::k_pwconv_bwd_data_tc), (size_t)smem);
     if (e != cudaSuccess) return e;
     tc::k_pwconv_bwd_data_tc<<<ntiles < 148 ? ntiles : 148, tc::kBdWarps * 32, smem, st>>>(grad_hwcp, weight, grad_x, Cin, Cout,
                                                                                          Cp, H, W, tiles_per_img, ntiles);
@@ -1094,7 +1094,7 @@ cudaError_t launch_pwconv_bwd_data(const float* grad_hwcp, const float* weight, 
   dim3 grid((unsigned)((HW + kPx - 1) / kPx), (unsigned)BV, (unsigned)((Cin + kKn - 1) / kKn));
   const bool vec = (HW % 4 == 0) && aligned16(grad_x);
   auto kern = vec ? k_pwconv_bwd_data<true> : k_pwconv_bwd_data<false>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdDataSmem);
+  cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(kern), (size_t)kBwdDataSmem);
   if (e != cudaSuccess) return e;
   // more than 32 output channels: one pass per 32-channel block of G, later passes add into grad_x
   for (int co0 = 0; co0 < Cout; co0 += kCo)
@@ -1114,7 +1114,7 @@ cudaError_t launch_pwconv_bwd_weight(const float* x, const float* grad_hwcp, flo
     float* pw = static_cast<float*>(ws);
     float* pb = pw + (size_t)nctas * CinPad * Cp;
     const int smem = (int)tc::bw_smem_bytes();
-    cudaError_t e = cudaFuncSetAttribute(tc::k_pwconv_bwd_weight_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(&tc::k_pwconv_bwd_weight_tc), (size_t)smem);
     if (e != cudaSuccess) return e;
     tc::k_pwconv_bwd_weight_tc<<<nctas, tc::kBwWarps * 32, smem, st>>>(x, grad_hwcp, pw, pb, Cin, Cp, H, W, chunks_per_img,
                                                                       nchunks, CinPad);
@@ -1127,7 +1127,7 @@ cudaError_t launch_pwconv_bwd_weight(const float* x, const float* grad_hwcp, flo
   dim3 grid((unsigned)nw, (unsigned)(CinPad / kKn), (unsigned)(Cp / kCo));
   const bool vec = (HW % 4 == 0) && aligned16(x);
   auto kern = vec ? k_pwconv_bwd_weight<true> : k_pwconv_bwd_weight<false>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdWeightSmem);
+  cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(kern), (size_t)kBwdWeightSmem);
   if (e != cudaSuccess) return e;
   kern<<<grid, 256, kBwdWeightSmem, st>>>(x, grad_hwcp, part_w, part_b, Cin, Cout, Cp, H, W, nchunk, total, CinPad);
   dim3 rgrid((unsigned)(Cin + 1), (unsigned)(Cp / 32));

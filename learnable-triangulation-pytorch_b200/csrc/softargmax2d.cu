@@ -299,7 +299,7 @@ static bool sam2d_fast_ok(const void* a, const void* b, const void* c, int H, in
 static int sam2d_threads(int n4) { return n4 <= 4096 ? 256 : 1024; }
 template <typename K>
 static cudaError_t sam2d_allow_smem(K kernel) {
-  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kS2MaxSmem);
+  return smem_opt_in(reinterpret_cast<const void*>(kernel), kS2MaxSmem);
 }
 
 cudaError_t launch_softargmax2d_fwd(const float* hm, float* coords, float* prob, int BJ, int H, int W, int softmax,

@@ -362,20 +362,20 @@ __global__ void k_conf_reduce(const float* __restrict__ part, float* __restrict_
 
 template <int LPV>
 static cudaError_t launch_bwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
-  const bool aligned = (a.N2 % kRun) == 0;
+  const bool aligned = (a.N2 % kRun) == 0 && (reinterpret_cast<uintptr_t>(a.gout) & 31u) == 0;
   const dim3 block(kWarpsPerCta * 32);
   constexpr int SL = TileGeom<LPV>::kSlots;
   constexpr size_t smem = sizeof(float4) * kMaxViewsSmem * 3 + kWarpsPerCta * kViewChunk * SL * (sizeof(float4) + sizeof(int)) +
                           sizeof(float4) * kWarpsPerCta * kRun * 32;
-#define LT_LAUNCH(K, AGG_)                                                                              \
-  do {                                                                                                  \
-    if (aligned) {                                                                                      \
-      cudaFuncSetAttribute(K<LPV, AGG_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
-      K<LPV, AGG_, true><<<grid, block, smem, st>>>(a);                                                 \
-    } else {                                                                                            \
-      cudaFuncSetAttribute(K<LPV, AGG_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-      K<LPV, AGG_, false><<<grid, block, smem, st>>>(a);                                                \
-    }                                                                                                   \
+#define LT_LAUNCH(K, AGG_)                                                                    \
+  do {                                                                                        \
+    if (aligned) {                                                                            \
+      LT_SMEM_OPT_IN_ONCE((K<LPV, AGG_, true>), smem);                                        \
+      K<LPV, AGG_, true><<<grid, block, smem, st>>>(a);                                       \
+    } else {                                                                                  \
+      LT_SMEM_OPT_IN_ONCE((K<LPV, AGG_, false>), smem);                                       \
+      K<LPV, AGG_, false><<<grid, block, smem, st>>>(a);                                      \
+    }                                                                                         \
   } while (0)
   switch (agg) {
     case kAggSum: LT_LAUNCH(k_unproject_bwd, kAggSum); break;
@@ -394,8 +394,11 @@ static cudaError_t launch_bwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaS
   return cudaGetLastError();
 }
 
-size_t unproject_bwd_ws_bytes(int B, int V, int C, int, int, int) {
-  return (size_t)B * kConfSlots * V * C * sizeof(float);
+size_t unproject_bwd_ws_bytes(int B, int V, int C, int N0, int N1, int N2) {
+  const size_t scatter = (size_t)B * kConfSlots * V * C * sizeof(float);
+  const UnprojShape s{B, V, C, 0, 0, N0, N1, N2, kAggConf, 0};
+  const size_t tile = unproject_bwd_tile_ws_bytes(s);  // whichever kernel the launch picks, the buffer is big enough
+  return scatter > tile ? scatter : tile;
 }
 
 cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, const float* proj,
@@ -415,9 +418,14 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
   }
   if (s.B == 0 || s.C == 0 || a.nvox == 0 || s.V == 0) return cudaSuccess;
   a.gconf_part = nullptr;
+  if (unproject_bwd_tile_eligible(s, grad_out)) {
+    // on-chip merged formulation (unproject_bwd_tile.cu); its grad_conf partials need no zero-fill
+    if (want_gconf && s.agg == kAggConf) a.gconf_part = static_cast<float*>(conf_ws);
+    return launch_unproject_bwd_tile(a, s, grad_conf, st);
+  }
   if (want_gconf && s.agg == kAggConf) {
     a.gconf_part = static_cast<float*>(conf_ws);
-    cudaError_t e = cudaMemsetAsync(conf_ws, 0, unproject_bwd_ws_bytes(s.B, s.V, s.C, 0, 0, 0), st);
+    cudaError_t e = cudaMemsetAsync(conf_ws, 0, (size_t)s.B * kConfSlots * s.V * s.C * sizeof(float), st);
     if (e != cudaSuccess) return e;
   }
   const int lpv = unproj_lpv(a.Cp);

@@ -260,20 +260,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
 
 template <int LPV>
 static cudaError_t launch_fwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
-  const bool aligned = (a.N2 % kRun) == 0;
+  const bool aligned = (a.N2 % kRun) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 31u) == 0;
   const dim3 block(kWarpsPerCta * 32);
   constexpr int SL = TileGeom<LPV>::kSlots;
   constexpr size_t smem = sizeof(float4) * kMaxViewsSmem * 3 + kWarpsPerCta * kViewChunk * SL * (sizeof(float4) + sizeof(int)) +
                           sizeof(float4) * kWarpsPerCta * kRun * 32;
-#define LT_LAUNCH(AGG_)                                                                                    \
-  do {                                                                                                     \
-    if (aligned) {                                                                                         \
-      cudaFuncSetAttribute(k_unproject_fwd<LPV, AGG_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
-      k_unproject_fwd<LPV, AGG_, true><<<grid, block, smem, st>>>(a);                                      \
-    } else {                                                                                               \
-      cudaFuncSetAttribute(k_unproject_fwd<LPV, AGG_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-      k_unproject_fwd<LPV, AGG_, false><<<grid, block, smem, st>>>(a);                                     \
-    }                                                                                                      \
+#define LT_LAUNCH(AGG_)                                                           \
+  do {                                                                            \
+    if (aligned) {                                                                \
+      LT_SMEM_OPT_IN_ONCE((k_unproject_fwd<LPV, AGG_, true>), smem);              \
+      k_unproject_fwd<LPV, AGG_, true><<<grid, block, smem, st>>>(a);             \
+    } else {                                                                      \
+      LT_SMEM_OPT_IN_ONCE((k_unproject_fwd<LPV, AGG_, false>), smem);             \
+      k_unproject_fwd<LPV, AGG_, false><<<grid, block, smem, st>>>(a);            \
+    }                                                                             \
   } while (0)
   switch (agg) {
     case kAggSum: LT_LAUNCH(kAggSum); break;
