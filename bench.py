@@ -43,7 +43,7 @@ WORKLOADS = {
     "cfg4": dict(B=8, V=31, C=32, H=96, W=96, N=64, J=17, agg="conf", scaling="strong",
                  desc="many-view stress: B=8 total (batch-sharded), 31 views, conf aggregation, fwd+bwd"),
     "cfg5": dict(B=1, V=4, C=32, H=96, W=96, N=256, J=17, agg="softmax", scaling="strong",
-                 desc="high-resolution volume: B=1, 4 views, 256^3 split into z-slabs, one NCCL exchange, fwd only K1 + fwd/bwd K2"),
+                 desc="high-resolution volume: B=1, 4 views, 256^3 split into z-slabs along the first volume axis; K1 fwd+bwd slab-local, K2 fwd with ONE NCCL all_gather of the (B,J,5) soft-argmax tuples at world > 1, K2 bwd slab-local"),
 }
 
 
@@ -238,6 +238,8 @@ class E2EStep:
     (two device input sets, events in both directions); the ops themselves run on torch's current stream through
     lt_b200.unproject_heatmaps / lt_b200.integrate_tensor_3d_with_coordinates under autograd."""
 
+    DEPTH = 3   # device input sets: the one being computed on + two prefetched (prefetch depth 2)
+
     def __init__(self, dstep):
         h, w = dstep.host, dstep.w
         self.w, self.dev = w, dstep.dev
@@ -249,26 +251,36 @@ class E2EStep:
                 "target": torch.zeros(dstep.B, w["J"], 3)}
         if h["vol_confidences"] is not None:
             host["conf"] = h["vol_confidences"]
-        self.host = {k: v.pin_memory() for k, v in host.items()}
-        self.dbuf = [{k: torch.empty(v.shape, device=self.dev) for k, v in self.host.items()} for _ in range(2)]
-        self.copied = [torch.cuda.Event() for _ in range(2)]
-        self.consumed = [torch.cuda.Event() for _ in range(2)]
+        # ONE pinned staging buffer and ONE device buffer per input set: a step's inputs travel as a single
+        # cudaMemcpyAsync (every tensor starts on a 256-byte boundary inside it); the named tensors are views.
+        offs, total = {}, 0
+        for k, v in host.items():
+            offs[k] = total
+            total += (v.numel() + 63) // 64 * 64
+        self.h_flat = torch.empty(total, dtype=torch.float32).pin_memory()
+        self.host = {}
+        for k, v in host.items():
+            self.host[k] = self.h_flat[offs[k]:offs[k] + v.numel()].view(v.shape)
+            self.host[k].copy_(v)
+        self.d_flat = [torch.empty(total, device=self.dev) for _ in range(self.DEPTH)]
+        self.dbuf = [{k: f[offs[k]:offs[k] + v.numel()].view(v.shape) for k, v in host.items()} for f in self.d_flat]
+        self.copied = [torch.cuda.Event() for _ in range(self.DEPTH)]
+        self.consumed = [torch.cuda.Event() for _ in range(self.DEPTH)]
         self.copy_stream = torch.cuda.Stream(device=self.dev)
         self.h_loss = torch.zeros(1).pin_memory()
         self.h_coords = torch.zeros(dstep.B, w["J"], 3).pin_memory()
-        self.h2d = sum(t.numel() * 4 for t in self.host.values())
+        self.h2d = total * 4
         self.d2h = (self.h_loss.numel() + self.h_coords.numel()) * 4
         self.issued = 0   # copies issued so far
         self.done = 0     # steps computed so far
         self.graphs = None
 
     def _issue_copy(self):
-        k = self.issued % 2
+        k = self.issued % self.DEPTH
         with torch.cuda.stream(self.copy_stream):
-            if self.issued >= 2:
+            if self.issued >= self.DEPTH:
                 self.copy_stream.wait_event(self.consumed[k])   # the step that used this set has finished
-            for name, src in self.host.items():
-                self.dbuf[k][name].copy_(src, non_blocking=True)
+            self.d_flat[k].copy_(self.h_flat, non_blocking=True)
             self.copied[k].record(self.copy_stream)
         self.issued += 1
 
@@ -305,15 +317,13 @@ class E2EStep:
             side = torch.cuda.Stream(device=self.dev)
             side.wait_stream(cur)
             with torch.cuda.stream(side):          # warm-up off the default stream, as torch.cuda.graph requires
-                for k in range(2):
-                    self.dbuf[k]["feat"].normal_()
-                    for name in ("proj", "spec"):
-                        self.dbuf[k][name].copy_(self.host[name], non_blocking=True)
+                for k in range(self.DEPTH):
+                    self.d_flat[k].copy_(self.h_flat, non_blocking=True)
                     self._compute(k)
             cur.wait_stream(side)
             torch.cuda.synchronize()
             graphs = []
-            for k in range(2):
+            for k in range(self.DEPTH):
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g):
                     self._compute(k)
@@ -327,10 +337,9 @@ class E2EStep:
         return self.graphs is not None
 
     def run(self):
-        if self.issued == self.done:      # nothing in flight (first step): this step's own copy
+        while self.issued < self.done + self.DEPTH:   # this step's own copy (first step) + the prefetches behind it
             self._issue_copy()
-        self._issue_copy()                # prefetch the next step's inputs while this one computes
-        k = self.done % 2
+        k = self.done % self.DEPTH
         cur = torch.cuda.current_stream()
         cur.wait_event(self.copied[k])
         if self.graphs is not None:
@@ -384,11 +393,96 @@ def bench_process_features(step, w, B, peak, iters=20):
     return res
 
 
-def cpu_reference_step(w, seed=0, cache={}):
-    """fwd+bwd of unproject_heatmaps and integrate_tensor_3d_with_coordinates for ONE batch item with the oracle's
-    restatement of mvn/utils/op.py (same ATen calls as the reference) on all host cores. Returns seconds."""
-    from lt_b200 import synthetic
+def bench_sharded_softargmax(rank, world, dev, steps=30, N=256, J=17):
+    """BASELINE config 5's soft-argmax across the ranks of this launch, the one path of the product with a collective:
+    every rank holds a slab of ONE (1, J, N, N, N) volume (split along the first volume axis), computes its (m, S, Sxyz)
+    tuples (lt_softargmax_partial), exchanges them with ONE all_gather_into_tensor (NCCL, B*J*5 floats per rank), merges
+    in rank order (lt_softargmax_merge) and normalises its slab (lt_softargmax_finalize). Timed with CUDA events on the
+    launching stream, max over ranks; the exchange has its own event pair. Parity: the coordinates against the
+    unsharded lt_softargmax_fwd of the same volume on this GPU (max |diff| in mm; bar 1e-3), and the slab of
+    probabilities against the unsharded ones (max-norm relative; bar 1e-5). Reported beside the path, never in `value`."""
+    import torch.distributed as dist
+    from lt_b200 import _lib, slab, volumetric
+    L, p, chk = _lib.lib(), _lib.ptr, _lib.check
+    st = torch.cuda.current_stream().cuda_stream
+    g = torch.Generator(device=dev).manual_seed(1234)              # identical on every rank
+    x = torch.randn((1, J, N, N, N), generator=g, device=dev)
+    spec = volumetric.coord_volume_specs([[10.0, -20.0, 30.0]], 2500.0, (N, N, N), [0.7])
+    coord = volumetric.coord_volumes_from_specs(spec.to(dev), (N, N, N))
+    lo, hi = slab.slab_bounds(N, world, rank)
+    xs, cs = x[:, :, lo:hi].contiguous(), coord[:, lo:hi].contiguous()
+    nvox_s, nvox = (hi - lo) * N * N, N * N * N
+    stats, merged = torch.empty((1, J, 5), device=dev), torch.empty((1, J, 5), device=dev)
+    parts = torch.empty((world, 1, J, 5), device=dev)
+    coords, prob = torch.empty((1, J, 3), device=dev), torch.empty_like(xs)
+    ws = torch.empty((max(L.lt_softargmax_ws_bytes(1, J, nvox), 4) // 4,), device=dev)
+
+    def step(ev=None):
+        chk(L.lt_softargmax_partial(p(xs), p(cs), p(stats), p(ws), 1, J, nvox_s, 1, 1.0, st))
+        if ev is not None:
+            ev[0].record()
+        dist.all_gather_into_tensor(parts.view(-1), stats.view(-1))
+        if ev is not None:
+            ev[1].record()
+        chk(L.lt_softargmax_merge(p(parts), p(merged), world, J, 1, st))
+        chk(L.lt_softargmax_finalize(p(xs), p(merged), p(coords), p(prob), 1, J, nvox_s, 1, 1.0, st))
+
+    for _ in range(3):
+        step()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    t0.record()
+    for i in range(steps):
+        step(evs[i])
+    t1.record()
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    t = torch.tensor([t0.elapsed_time(t1), sum(a.elapsed_time(b) for a, b in evs)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    # parity against the unsharded op on this GPU
+    c_full, p_full, s_full = torch.empty((1, J, 3), device=dev), torch.empty_like(x), torch.empty((1, J, 5), device=dev)
+    chk(L.lt_softargmax_fwd(p(x), p(coord), p(c_full), p(p_full), p(s_full), p(ws), 1, J, nvox, 1, 1.0, st))
+    err = torch.stack([(coords - c_full).abs().max(),
+                       (prob - p_full[:, :, lo:hi]).abs().max() / p_full.abs().max()])
+    dist.all_reduce(err, op=dist.ReduceOp.MAX)
+    ms = t[0].item() / steps
+    return {"workload": "cfg5 K2 forward, ONE (1,%d,%d^3) volume in %d z-slabs" % (J, N, world), "ranks": world,
+            "steps": steps, "ms_per_step": round(ms, 4), "volumes_per_s": round(1e3 / ms, 1),
+            "exchange": {"op": "all_gather_into_tensor (NCCL)", "bytes_per_rank": J * 5 * 4,
+                         "us_per_step": round(t[1].item() / steps * 1e3, 1)},
+            "parity": {"max_abs_coord_diff_mm": err[0].item(), "max_rel_prob_diff": err[1].item(),
+                       "against": "unsharded lt_softargmax_fwd of the same volume on each rank's GPU"}}
+
+
+def reference_ops():
+    """(module with unproject_heatmaps / integrate_tensor_3d_with_coordinates, kind): the UNMODIFIED reference
+    (`mvn.utils.op` from /root/reference or its verbatim copy oracle/_ref, see oracle/fetch_ref.py) when present
+    -> "reference"; else the oracle's restatement of the same functions -> "port"."""
+    import warnings
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    try:
+        from fetch_ref import ref_path
+        rp = ref_path()
+        if rp is not None:
+            sys.path.insert(0, rp)
+            try:
+                from mvn.utils import op as ref_op
+                warnings.filterwarnings("ignore", message=".*grid_sample.*")
+                return ref_op, "reference"
+            except Exception as e:  # noqa: BLE001
+                sys.stderr.write("reference import failed (%s); timing the oracle port instead\n" % e)
+    finally:
+        sys.path.remove(os.path.join(ROOT, "oracle"))
     from oracle import ref_ops
+    return ref_ops, "port"
+
+
+def cpu_reference_step(w, seed=0, cache={}):
+    """fwd+bwd of unproject_heatmaps and integrate_tensor_3d_with_coordinates for ONE batch item on all host cores with
+    the reference's own functions (mvn/utils/op.py:84-163, unmodified) or, where its tree is absent, the oracle's
+    restatement of them (same ATen calls). Returns seconds."""
+    from lt_b200 import synthetic
+    ref_ops = reference_ops()[0]
     key = (w["V"], w["C"], w["N"], w["agg"], seed)
     if key not in cache:
         conf = "conf" if w["agg"] == "conf" else None
@@ -416,7 +510,7 @@ def run_cpu_arm(w, steps, warmup):
         cpu_reference_step(w)
     times = [cpu_reference_step(w) for _ in range(steps)]
     total = sum(times)
-    return steps / total, total / steps, torch.get_num_threads()
+    return steps / total, total / steps, torch.get_num_threads(), reference_ops()[1]
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -438,7 +532,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     metric = "volumes/sec fwd+bwd (unproject+aggregate + soft-argmax, %d^3, %d views, %dch)" % (w["N"], w["V"], w["C"])
     config = {"workload": "%s: %s" % (args.workload, w["desc"]), "aggregation": w["agg"], "joints": w["J"],
-              "parallelism": "batch-sharded x%d, no data-path collective" % world,
+              "parallelism": ("z-slabs of ONE 256^3 volume x%d ranks, one all_gather_into_tensor of %d bytes per rank and "
+                              "step (NCCL) in K2 forward" % (world, 1 * w["J"] * 5 * 4) if args.workload == "cfg5" and world > 1
+                              else "batch-sharded x%d, no data-path collective" % world),
               "cache": None}
     _ab = algorithmic_bytes(w, w["B"])
     config["cache"] = ("inputs larger than L2 (per-step working set %.0f MB >> 126 MB L2)" % (sum(_ab.values()) / 2e6)
@@ -450,13 +546,15 @@ def main():
         if rank != 0:
             return
         steps = max(1, min(args.steps, 8))
-        vps, sec, cores = run_cpu_arm(w, steps, max(1, min(args.warmup, 1)))
+        vps, sec, cores, kind = run_cpu_arm(w, steps, max(1, min(args.warmup, 1)))
+        what = ("the reference's own mvn/utils/op.py functions, unmodified (oracle/_ref)" if kind == "reference" else
+                "oracle port of mvn/utils/op.py (the reference tree is absent)")
         line = {"impl": "reference", "metric": metric, "value": vps, "unit": "volumes/s", "n_gpus": args.gpus,
                 "steps": steps, "warmup": 1, "ms_per_step": sec * 1e3, "higher_is_better": True,
                 "scaling": w["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-                "cpu_baseline": {"value": vps, "unit": "volumes/s", "cores": cores, "kind": "port",
-                                 "sample": "%d x one batch item (B=1) fwd+bwd, oracle port of mvn/utils/op.py on torch "
-                                           "CPU; the python reference tree does not travel to the GPU box" % steps},
+                "cpu_baseline": {"value": vps, "unit": "volumes/s", "cores": cores, "kind": kind,
+                                 "sample": "%d x one batch item (B=1) fwd+bwd on torch CPU, all host threads: %s"
+                                           % (steps, what)},
                 "e2e": {"value": vps, "unit": "volumes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         print(json.dumps(line))
@@ -564,6 +662,15 @@ def main():
         except Exception as exc:  # a side measurement must never cost the bench line
             roofline["next_rows"] = {"k7_process_features": {"error": repr(exc)[:200]}}
 
+    # the one collective of the product (cfg5's z-slab soft-argmax), measured on the ranks of THIS launch with a parity
+    # number, whatever the workload: the default multi-GPU line (cfg3) has no collective of its own
+    if world > 1:
+        try:
+            rec = bench_sharded_softargmax(rank, world, dev)
+        except Exception as exc:  # noqa: BLE001 - a side measurement must never cost the bench line
+            rec = {"error": repr(exc)[:200]}
+        roofline.setdefault("next_rows", {})["cfg5_sharded_softargmax"] = rec
+
     e2e = None
     if not args.no_e2e:
         es = E2EStep(step)
@@ -574,16 +681,18 @@ def main():
                "d2h_bytes_per_step": es.d2h, "steps": e_steps, "ms_per_step": ems / e_steps, "cuda_graph": graphed,
                "note": "public python ops under autograd (captured once into a CUDA graph per input set when cuda_graph is "
                        "true, replayed every step); pinned-host inputs (feature maps, projection matrices, "
-                       "18-float cuboid specs) copied every step on a second stream (prefetch depth 1), coordinate "
+                       "18-float cuboid specs) staged in ONE pinned buffer and copied every step with one cudaMemcpyAsync on a "
+                       "second stream (prefetch depth 2), coordinate "
                        "volumes built on the device as triangulation.py:280-341 does, loss + coordinates read back "
                        "every step"}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        vps, sec, cores = run_cpu_arm(w, 5, 1)
-        cpu_baseline = {"value": vps, "unit": "volumes/s", "cores": cores, "kind": "port",
-                        "sample": "5 x one batch item (B=1) fwd+bwd of the same workload, oracle port of "
-                                  "mvn/utils/op.py (torch CPU, all host threads)"}
+        vps, sec, cores, kind = run_cpu_arm(w, 5, 1)
+        cpu_baseline = {"value": vps, "unit": "volumes/s", "cores": cores, "kind": kind,
+                        "sample": "5 x one batch item (B=1) fwd+bwd of the same workload on torch CPU, all host threads: "
+                                  + ("the reference's own mvn/utils/op.py functions, unmodified (oracle/_ref)"
+                                     if kind == "reference" else "oracle port of mvn/utils/op.py")}
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": "volumes/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,

@@ -22,6 +22,12 @@
  *     bad arguments. lt_last_error() returns a thread-local message for the last non-zero return.
  *     Nothing throws across this boundary.
  *   - there is no CPU implementation behind any entry point.
+ *   - alignment: every pointer must be aligned to its element type (4 bytes for float/int, 8 for double). Pointers
+ *     from cudaMalloc / torch's allocator are 256-byte aligned and take the vector paths; a pointer that is only
+ *     element-aligned (a view with an odd storage offset) is legal and takes scalar paths: the launchers test the
+ *     16/32-byte alignment of every tensor they access with vector instructions. Exceptions, which are REQUIRED to
+ *     be 16-byte aligned and rejected with LT_ERR_INVALID otherwise: proj (rows are read as float4), the hwcp
+ *     buffers of K0/K1/K7 (texels are read and reduced as float4) and every workspace.
  */
 #ifndef LT_B200_H
 #define LT_B200_H
@@ -170,8 +176,10 @@ int lt_softargmax_bwd_add_sparse(const float *prob, const int *idx, const float 
  * overwritten, summed in a fixed order (deterministic).  ws: lt_pwconv_ws_bytes() bytes of scratch, 16-byte aligned
  * (forward and backward-weight; may be shared, contents are not kept between calls).
  * At the reference's shape (Cout <= 32, Cin = 128 or 256, H*W a multiple of 32, x 16-byte and out_hwcp 32-byte aligned)
- * all three run on the tcgen05 tensor cores with a three-product TF32 split (fp32 accuracy); other shapes and alignments
- * run fp32 FMA kernels with the same results to 2e-6. */
+ * all three run on the tcgen05 tensor cores with a three-product TF32 split: operands are truncated to hi (19 bits) +
+ * lo and the lo*lo product is dropped, measured 1-2e-6 relative (max-norm) against an fp64 convolution, i.e. the level
+ * of an fp32 FMA chain but NOT bit-identical to one; other shapes and alignments run fp32 FMA kernels (same results to
+ * 2e-6). */
 size_t lt_pwconv_ws_bytes(int BV, int Cin, int Cout, int H, int W);
 int lt_pwconv_fwd(const float *x, const float *weight, const float *bias, float *out_hwcp, void *ws,
                   int BV, int Cin, int Cout, int H, int W, void *stream);

@@ -36,6 +36,9 @@ bool bad_unproj_shape(int B, int V, int C, int H, int W, int N0, int N1, int N2)
     if (!(cond)) return fail_invalid(__func__, msg); \
   } while (0)
 
+// buffers the kernels only ever access as float4 (include/lt_b200.h "alignment")
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
 #define LT_API __attribute__((visibility("default")))
 extern "C" {
 
@@ -50,6 +53,7 @@ LT_API int lt_feat_to_hwc(const float* src_chw, float* dst_hwc, int BV, int C, i
   LT_REQUIRE(BV <= 65535, "B*V > 65535");
   if ((long long)BV * C * H * W == 0) return 0;
   LT_REQUIRE(src_chw && dst_hwc, "null pointer");
+  LT_REQUIRE(al16(dst_hwc), "the hwcp buffer must be 16-byte aligned");
   return finish(__func__, lt::launch_feat_layout(src_chw, dst_hwc, BV, C, H, W, true, as_stream(stream)));
 }
 
@@ -58,6 +62,7 @@ LT_API int lt_feat_to_chw(const float* src_hwc, float* dst_chw, int BV, int C, i
   LT_REQUIRE(BV <= 65535, "B*V > 65535");
   if ((long long)BV * C * H * W == 0) return 0;
   LT_REQUIRE(src_hwc && dst_chw, "null pointer");
+  LT_REQUIRE(al16(src_hwc), "the hwcp buffer must be 16-byte aligned");
   return finish(__func__, lt::launch_feat_layout(src_hwc, dst_chw, BV, C, H, W, false, as_stream(stream)));
 }
 
@@ -68,6 +73,7 @@ LT_API int lt_unproject_fwd(const float* feat_hwc, const float* proj, const floa
   LT_REQUIRE(agg >= LT_AGG_SUM && agg <= LT_AGG_SOFTMAX, "unknown aggregation");
   if ((long long)B * C * N0 * N1 * N2 == 0) return 0;
   LT_REQUIRE(feat_hwc && proj && coord && out, "null pointer");
+  LT_REQUIRE(al16(feat_hwc) && al16(proj), "feat_hwc and proj must be 16-byte aligned");
   LT_REQUIRE(agg != LT_AGG_CONF || conf, "conf aggregation needs vol_confidences");
   lt::UnprojShape s{B, V, C, H, W, N0, N1, N2, agg, align_corners ? 1 : 0};
   return finish(__func__, lt::launch_unproject_fwd(feat_hwc, proj, coord, conf, out, s, as_stream(stream)));
@@ -85,6 +91,8 @@ LT_API int lt_unproject_bwd(const float* grad_out, const float* feat_hwc, const 
   LT_REQUIRE(agg >= LT_AGG_SUM && agg <= LT_AGG_SOFTMAX, "unknown aggregation");
   if ((long long)B * C == 0) return 0;
   LT_REQUIRE(feat_hwc && proj && coord && grad_feat_hwc, "null pointer");
+  LT_REQUIRE(al16(feat_hwc) && al16(proj) && al16(grad_feat_hwc) && al16(conf_ws),
+             "feat_hwc, proj, grad_feat_hwc and conf_ws must be 16-byte aligned");
   LT_REQUIRE((long long)N0 * N1 * N2 == 0 || grad_out, "null grad_out");
   LT_REQUIRE(agg != LT_AGG_CONF || conf, "conf aggregation needs vol_confidences");
   LT_REQUIRE(!(agg == LT_AGG_CONF && grad_conf) || conf_ws, "grad_conf needs conf_ws");

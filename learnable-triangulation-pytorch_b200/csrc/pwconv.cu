@@ -394,7 +394,8 @@ constexpr int kGroups = 3, kProducerWarps = 4 * kGroups, kMmaWarp = kProducerWar
 constexpr int kRawDepth = 3;   // raw stages in flight per producer group (16 KB each)
 constexpr uint32_t kLboB = 128;                          // W tile: [channel group of 8][k4][8 channels][16 B]
 constexpr uint32_t idesc_tf32(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kM >> 4) << 24); }
-constexpr uint32_t kSpinLimit = 1u << 27;
+constexpr uint32_t kSpinLimit = 1u << 16;          // fast polls before backing off
+constexpr uint64_t kWaitLimitNs = 20ull * 1000000000ull;
 constexpr uint32_t kAccCols = 3 * kN, kRingCol0 = 2 * kAccCols, kStageCols = 2 * kKs, kTmemCols = 512;
 static_assert(kRingCol0 + kStagesTc * kStageCols <= kTmemCols, "TMEM map");
 
@@ -405,16 +406,29 @@ __device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* b) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
-// bounded spin: a protocol error traps (the launch fails loudly) instead of hanging the GPU
+// bounded wait: a protocol error traps (the launch fails loudly) instead of hanging the GPU. The bound is TIME, not a
+// poll count: after kSpinLimit fast polls the waiter backs off with nanosleep and only traps once the barrier has been
+// stuck for kWaitLimitNs of wall clock (20 s), so a legitimately long stall (debugger, sanitizer, preemption) is not
+// turned into a sticky context error.
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
   const uint32_t a = smem_u32(b);
-  for (uint32_t i = 0; i < kSpinLimit; ++i) {
+  uint64_t t0 = 0;
+  for (uint32_t i = 0;; ++i) {
     uint32_t done;
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
                  : "=r"(done) : "r"(a), "r"(parity) : "memory");
     if (done) return;
+    if (i >= kSpinLimit) {
+      if (t0 == 0) t0 = globaltimer_ns();
+      __nanosleep(256);
+      if ((i & 0x3ffu) == 0 && globaltimer_ns() - t0 > kWaitLimitNs) __trap();
+    }
   }
-  __trap();
 }
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
   return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
@@ -1030,7 +1044,17 @@ inline bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 constexpr int kFwdSmem = kStages * (kKc * kPx + kKc * kCo) * 4;      // 73,728 B -> 3 CTAs per SM
 constexpr int kBwdDataSmem = (kCo * kPx + kCo * kKn) * 4;            // 65,536 B -> 3 CTAs per SM
 constexpr int kBwdWeightSmem = kWgStages * kWgStageFloats * 4;       // 90,112 B -> 2 CTAs per SM
-constexpr int kWeightWorkers = 2 * 148;                              // persistent: 2 CTAs on each of the 148 SMs
+// SM count of the current device, queried once per device (148 on B200): the persistent kernels launch one CTA per SM
+int sm_count() {
+  static int cached[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    cached[dev] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
+  }
+  return cached[dev];
+}
 
 // developer knob for A/B measurements (tools/bench_process_features.py): LT_B200_PWCONV=ffma keeps the forward on the
 // FMA pipe. Read once; both paths compute the same fp32 result to 1e-6.
@@ -1041,7 +1065,8 @@ bool force_ffma() {
 
 int weight_workers(int BV, int H, int W) {   // an upper bound for both weight-gradient kernels (the tcgen05 one uses <= 148)
   const long long total = (long long)BV * ((H * W + kWgPx - 1) / kWgPx);
-  return (int)(total < kWeightWorkers ? total : kWeightWorkers);
+  const long long workers = 2LL * sm_count();  // persistent: 2 CTAs on every SM
+  return (int)(total < workers ? total : workers);
 }
 
 }  // namespace
@@ -1063,7 +1088,7 @@ cudaError_t launch_pwconv_fwd(const float* x, const float* weight, const float* 
     const int smem = (int)tc::smem_bytes(Cin);
     cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(&tc::k_pwconv_fwd_tc), (size_t)smem);
     if (e != cudaSuccess) return e;
-    tc::k_pwconv_fwd_tc<<<ntiles < 148 ? ntiles : 148, tc::kWarps * 32, smem, st>>>(x, weight, bias, out_hwcp, Cin, Cout,
+    tc::k_pwconv_fwd_tc<<<ntiles < sm_count() ? ntiles : sm_count(), tc::kWarps * 32, smem, st>>>(x, weight, bias, out_hwcp, Cin, Cout,
                                                                                   Cp, H, W, tiles_per_img, ntiles);
     return cudaGetLastError();
   }
@@ -1087,7 +1112,7 @@ cudaError_t launch_pwconv_bwd_data(const float* grad_hwcp, const float* weight, 
     const int smem = (int)tc::bd_smem_bytes(Cin);
     cudaError_t e = smem_opt_in(reinterpret_cast<const void*>(&tc::k_pwconv_bwd_data_tc), (size_t)smem);
     if (e != cudaSuccess) return e;
-    tc::k_pwconv_bwd_data_tc<<<ntiles < 148 ? ntiles : 148, tc::kBdWarps * 32, smem, st>>>(grad_hwcp, weight, grad_x, Cin, Cout,
+    tc::k_pwconv_bwd_data_tc<<<ntiles < sm_count() ? ntiles : sm_count(), tc::kBdWarps * 32, smem, st>>>(grad_hwcp, weight, grad_x, Cin, Cout,
                                                                                          Cp, H, W, tiles_per_img, ntiles);
     return cudaGetLastError();
   }
@@ -1110,7 +1135,7 @@ cudaError_t launch_pwconv_bwd_weight(const float* x, const float* grad_hwcp, flo
   const int nw = weight_workers(BV, H, W);
   if (tc::bw_usable(Cin, Cout, HW) && aligned16(x) && !force_ffma()) {
     const int chunks_per_img = HW / tc::kBwPx, nchunks = BV * chunks_per_img;
-    const int nctas = nchunks < 148 ? nchunks : 148;
+    const int nctas = nchunks < sm_count() ? nchunks : sm_count();
     float* pw = static_cast<float*>(ws);
     float* pb = pw + (size_t)nctas * CinPad * Cp;
     const int smem = (int)tc::bw_smem_bytes();

@@ -378,6 +378,9 @@ size_t softargmax_ws_bytes(int B, int J, long long nvox) {
   return (size_t)B * J * sam_chunks(nvox) * kSamWarps * 5 * sizeof(float);
 }
 
+// the 128-bit paths need 16-byte aligned bases on top of nvox % 4 == 0 (include/lt_b200.h "alignment")
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
 cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,
                                       int J, long long nvox, int softmax, float mult, cudaStream_t st) {
   if (B * J == 0) return cudaSuccess;
@@ -385,7 +388,7 @@ cudaError_t launch_softargmax_partial(const float* vol, const float* coord, floa
     return launch_softargmax_merge(nullptr, stats, 0, B * J, softmax, st);
   }
   const int nchunk = sam_chunks(nvox);
-  const bool vec = (nvox % 4) == 0;
+  const bool vec = (nvox % 4) == 0 && al16(vol) && al16(coord);
   dim3 grid(nchunk, B);
   float* w = static_cast<float*>(ws);
 #define LT_GO(V_, S_) k_sam_stats<V_, S_><<<grid, kSamThreads, 0, st>>>(vol, coord, w, J, nvox, mult)
@@ -414,7 +417,7 @@ cudaError_t launch_softargmax_finalize(const float* vol, const float* stats, flo
                                        cudaStream_t st) {
   if (B * J == 0) return cudaSuccess;
   const int nchunk = nvox == 0 ? 1 : sam_chunks(nvox);
-  const bool vec = (nvox % 4) == 0;
+  const bool vec = (nvox % 4) == 0 && al16(vol) && al16(prob);
   dim3 grid(nchunk, B * J);
 #define LT_GO(V_, S_) k_sam_final<V_, S_><<<grid, kSamThreads, 0, st>>>(vol, stats, coords, prob, nvox, mult)
   if (vec) { if (softmax) LT_GO(true, true); else LT_GO(true, false); }
@@ -431,7 +434,7 @@ cudaError_t launch_softargmax_bwd_dot(const float* prob, const float* grad_prob,
   const int nchunk = sam_chunks(nvox);
   dim3 grid(nchunk, BJ);
   float* w = static_cast<float*>(ws);
-  if (nvox % 4 == 0) k_sam_dot<true><<<grid, kSamThreads, 0, st>>>(prob, grad_prob, w, nvox);
+  if (nvox % 4 == 0 && al16(prob) && al16(grad_prob)) k_sam_dot<true><<<grid, kSamThreads, 0, st>>>(prob, grad_prob, w, nvox);
   else k_sam_dot<false><<<grid, kSamThreads, 0, st>>>(prob, grad_prob, w, nvox);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
@@ -446,7 +449,8 @@ cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const f
                                   cudaStream_t st) {
   if (B * J == 0 || nvox == 0) return cudaSuccess;
   dim3 grid(sam_chunks(nvox), B);
-  const bool vec = (nvox % 4) == 0, gp = grad_prob != nullptr;
+  const bool gp = grad_prob != nullptr;
+  const bool vec = (nvox % 4) == 0 && al16(prob) && al16(coord) && al16(grad_vol) && (!gp || al16(grad_prob));
 #define LT_GO(V_, S_, G_) \
   k_sam_bwd<V_, S_, G_><<<grid, kSamThreads, 0, st>>>(prob, coord, coords, grad_coords, grad_prob, dots, grad_vol, J, nvox, mult)
   if (vec) {

@@ -48,20 +48,26 @@ struct BtCfg {
   static constexpr int ROUNDS = NRUNS / NG;
   static_assert(NRUNS % NG == 0 && ROUNDS >= 1, "runs must tile the lane groups");
   static_assert(RUN == 4 || RUN == 8, "run = one 128- or 256-bit load per channel");
-  static constexpr int NB = TV >= 256 ? 1024 : 512;  // histogram bins per view (keys beyond share the last bin)
+  static constexpr int NB = 512;             // histogram bins per view (keys beyond share the last bin)
+  static constexpr int PER = NB / 32;        // bins per lane in the scan
+  static constexpr int HS = 32 * (PER + 1);  // padded pitch of one view's histogram
+  __host__ __device__ static constexpr int hslot(int key) { return (key / PER) * (PER + 1) + key % PER; }
   static constexpr int NT = NW * 32;
   static constexpr int CTAS = TV >= 256 ? 1 : 2;
-  // shared-memory map (bytes)
-  static constexpr size_t oStage = 0;                                               // float4 [4][TV][8]
-  static constexpr size_t oW = oStage + (size_t)kViewChunk * TV * kCp * 4;          // float4 [4][TV]
-  static constexpr size_t oOff = oW + (size_t)kViewChunk * TV * 16;                 // int    [4][TV]
-  static constexpr size_t oKr = oOff + (size_t)kViewChunk * TV * 4;                 // int    [4][TV]  key | rank << 16
-  static constexpr size_t oHist = oKr + (size_t)kViewChunk * TV * 4;                // int    [4][NB]
-  static constexpr size_t oIdx = oHist + (size_t)kViewChunk * NB * 4;               // u16    [4][TV]
-  static constexpr size_t oProj = oIdx + (size_t)kViewChunk * TV * 2;               // float4 [4*3]
+  // shared-memory map (bytes). "rec" arrays hold the (voxel, view) records of all views in CELL-SORTED order, view after
+  // view; the voxel-order weights and key|rank words are only needed until the records are written and live in the
+  // stage (which is not touched before that).
+  static constexpr size_t oStage = 0;                                               // float4 [4][TV][8]  s, then d
+  static constexpr size_t oRecW = oStage + (size_t)kViewChunk * TV * kCp * 4;       // float4 [4*TV]  tap weights
+  static constexpr size_t oRecM = oRecW + (size_t)kViewChunk * TV * 16;             // int2   [4*TV]  (off | view, slot)
+  static constexpr size_t oOff = oRecM + (size_t)kViewChunk * TV * 8;               // int    [4][TV] voxel order
+  static constexpr size_t oHist = oOff + (size_t)kViewChunk * TV * 4;               // int    [4][HS]
+  static constexpr size_t oProj = oHist + (size_t)kViewChunk * HS * 4;              // float4 [4*3]
   static constexpr size_t oBox = oProj + (size_t)kViewChunk * 3 * 16;               // int4   [4]
   static constexpr size_t oN = oBox + (size_t)kViewChunk * 16;                      // int    [4]
   static constexpr size_t kBytes = oN + 32;
+  static constexpr size_t oW = oStage;                                              // float4 [4][TV] voxel order (temp)
+  static constexpr size_t oKr = oStage + (size_t)kViewChunk * TV * 16;              // int    [4][TV] key | rank << 16
 };
 
 // approximate heat-map position of a point (bounding box of the sort keys only; the taps come from make_taps)
@@ -82,9 +88,36 @@ __device__ __forceinline__ bool approx_ixy(float x, float y, float z, const floa
   return pz > 0.f && fabsf(ix) < 1.0e6f && fabsf(iy) < 1.0e6f;  // also false for nan
 }
 
-__device__ __forceinline__ bool nz4(const float4& v) { return v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f; }
-__device__ __forceinline__ void red4(float* p, const float4& v) {
-  if (nz4(v)) red_add_v4(p, v.x, v.y, v.z, v.w);
+__device__ __forceinline__ void red4(float* p, const float4& v) { red_add_v4(p, v.x, v.y, v.z, v.w); }
+
+// softmax aggregation over <= 4 views, derivative w.r.t. every view's sample, two channels per call:
+//   out = sum_v s_v p_v, p = softmax_v(s)  =>  d s_v = g * p_v * (1 + s_v - out)        (mvn/utils/op.py:154-159)
+// absent views carry kNoView (e -> 0 -> d = 0). Same operation order as the scalar form in unproject_bwd.cu.
+__device__ __forceinline__ void softmax_bwd4_x2(f2 s0, f2 s1, f2 s2, f2 s3, f2 g, f2 (&d)[4]) {
+  float a0, b0, a1, b1, a2, b2, a3, b3;
+  unpack2(s0, a0, b0); unpack2(s1, a1, b1); unpack2(s2, a2, b2); unpack2(s3, a3, b3);
+  const float ma = fmaxf(fmaxf(a0, a1), fmaxf(a2, a3)), mb = fmaxf(fmaxf(b0, b1), fmaxf(b2, b3));
+  const f2 L2 = pack2(kLog2eF, kLog2eF);
+  const f2 nm = mul2(pack2(-ma, -mb), L2);
+  const f2 sv[4] = {s0, s1, s2, s3};
+  f2 e[4];
+  f2 den = pack2(0.f, 0.f), num = pack2(0.f, 0.f);
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    float ta, tb;
+    unpack2(fma2(sv[v], L2, nm), ta, tb);
+    e[v] = pack2(fast_ex2(ta), fast_ex2(tb));
+    den = add2(den, e[v]);
+    num = fma2(sv[v], e[v], num);
+  }
+  float da, db;
+  unpack2(den, da, db);
+  const f2 inv = pack2(fast_rcp(da), fast_rcp(db));
+  const f2 one = pack2(1.f, 1.f), neg = pack2(-1.f, -1.f);
+  const f2 o1 = fma2(mul2(num, inv), neg, one);  // 1 - out
+  const f2 gi = mul2(g, inv);
+#pragma unroll
+  for (int v = 0; v < 4; ++v) d[v] = mul2(mul2(gi, e[v]), add2(o1, sv[v]));
 }
 __device__ __forceinline__ void fma4(float4& acc, float w, const float4& d) {
   acc.x = fmaf(w, d.x, acc.x); acc.y = fmaf(w, d.y, acc.y); acc.z = fmaf(w, d.z, acc.z); acc.w = fmaf(w, d.w, acc.w);
@@ -99,7 +132,8 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
   int* s_off = reinterpret_cast<int*>(smem + CF::oOff);
   int* s_kr = reinterpret_cast<int*>(smem + CF::oKr);
   int* s_hist = reinterpret_cast<int*>(smem + CF::oHist);
-  unsigned short* s_idx = reinterpret_cast<unsigned short*>(smem + CF::oIdx);
+  float4* s_rec_w = reinterpret_cast<float4*>(smem + CF::oRecW);
+  int2* s_rec_m = reinterpret_cast<int2*>(smem + CF::oRecM);
   float4* s_proj = reinterpret_cast<float4*>(smem + CF::oProj);
   int4* s_box = reinterpret_cast<int4*>(smem + CF::oBox);
   int* s_n = reinterpret_cast<int*>(smem + CF::oN);
@@ -126,7 +160,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
   for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
     const int nv = min(kViewChunk, a.V - v0);
     // ---------------- P0: histograms, projection rows, key bounding boxes ----------------
-    for (int i = tid; i < kViewChunk * NB / 4; i += NT) reinterpret_cast<int4*>(s_hist)[i] = make_int4(0, 0, 0, 0);
+    for (int i = tid; i < kViewChunk * CF::HS / 4; i += NT) reinterpret_cast<int4*>(s_hist)[i] = make_int4(0, 0, 0, 0);
     if (tid < nv * 3) s_proj[tid] = __ldg(reinterpret_cast<const float4*>(a.proj) + ((size_t)b * a.V + v0) * 3 + tid);
     __syncthreads();
     if (warp == 0) {
@@ -161,6 +195,99 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
     }
     __syncthreads();
 
+    // ---------------- A: descriptors + sort keys of every (voxel, view) of the tile ----------------
+    // thread <-> voxel in memory order (coalesced coordinate loads); the rank among equal keys comes from the atomic
+    for (int it = tid; it < nv * TV; it += NT) {
+      const int vox = it % TV, vv = it / TV;
+      const int run = vox / RUN, j = vox % RUN;
+      const int vi0 = t0 * CF::T0 + run / CF::T1, vi1 = t1 * CF::T1 + run % CF::T1, vz = z0 + j;
+      int off = -1, kr = 0;
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (vi0 < a.N0 && vi1 < a.N1 && vz < a.N2) {
+        const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
+        const float x = __ldg(cp), y = __ldg(cp + 1), z = __ldg(cp + 2);
+        int x0, y0;
+        if (make_taps(x, y, z, s_proj[vv * 3], s_proj[vv * 3 + 1], s_proj[vv * 3 + 2], a.H, a.W, invH, invW,
+                      a.align_corners, x0, y0, w)) {
+          off = ((y0 + 1) * (a.W + 2) + (x0 + 1)) * kCp;
+          const int4 bx = s_box[vv];
+          const int kx = min(max(x0 - bx.x, 0), bx.z - 1), ky = max(y0 - bx.y, 0);
+          const int key = min(ky * bx.z + kx, NB - 1);
+          const int rank = atomicAdd(&s_hist[vv * CF::HS + CF::hslot(key)], 1);
+          kr = key | (rank << 16);
+        }
+      }
+      s_w[it] = w;
+      s_off[it] = off;
+      s_kr[it] = kr;
+    }
+    __syncthreads();
+
+    // ---------------- S: exclusive scan of each view's histogram (warp vv; a lane owns PER consecutive bins, the
+    // padded pitch keeps both this walk and the random atomics above free of bank conflicts) ----------------
+    if (warp < nv) {
+      int* h = s_hist + warp * CF::HS + lane * (CF::PER + 1);
+      int vals[CF::PER];
+      int sum = 0;
+#pragma unroll
+      for (int i = 0; i < CF::PER; ++i) { vals[i] = h[i]; }
+#pragma unroll
+      for (int i = 0; i < CF::PER; ++i) { const int t_ = vals[i]; vals[i] = sum; sum += t_; }
+      int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+      }
+      const int excl = incl - sum;
+#pragma unroll
+      for (int i = 0; i < CF::PER; ++i) h[i] = vals[i] + excl;
+      if (lane == 31) s_n[warp] = incl;
+    }
+    __syncthreads();
+    // records in cell-sorted order, view after view: (texel offset | view, stage slot) + the four tap weights
+    const int b1 = s_n[0], b2 = b1 + (nv > 1 ? s_n[1] : 0), b3 = b2 + (nv > 2 ? s_n[2] : 0);
+    const int n_total = b3 + (nv > 3 ? s_n[3] : 0);
+    for (int it = tid; it < nv * TV; it += NT) {
+      const int off = s_off[it];
+      if (off >= 0) {
+        const int vv = it / TV, kr = s_kr[it];
+        const int pos = (vv == 0 ? 0 : (vv == 1 ? b1 : (vv == 2 ? b2 : b3))) +
+                        s_hist[vv * CF::HS + CF::hslot(kr & 0xffff)] + (kr >> 16);
+        s_rec_m[pos] = make_int2(off | vv, it);  // off is a multiple of Cp = 32: the low bits are free
+        s_rec_w[pos] = s_w[it];
+      }
+    }
+    __syncthreads();
+    const int chunk = (n_total + NG - 1) / NG;
+    const int gid = warp * kG + g;
+    const int rec_begin = min(n_total, gid * chunk), rec_end = min(n_total, rec_begin + chunk);
+    const float* fbv = fb + (size_t)v0 * viewStride;
+    float* gbv = gb + (size_t)v0 * viewStride;
+
+    // ---------------- G: samples, gathered in CELL-SORTED order: consecutive records read the same or neighbouring
+    // texels, so all but the first touch of a texel hit L1 ----------------
+    if (AGG != kAggSum) {
+      int rec = rec_begin;
+#pragma unroll 1
+      for (; rec + 1 < rec_end; rec += 2) {
+        const int2 ma = s_rec_m[rec], mb = s_rec_m[rec + 1];
+        float sa[kCPL], sb[kCPL];
+        gather4(fbv + (size_t)(ma.x & 3) * viewStride, ma.x & ~3, s_rec_w[rec], kCp, rowStride, sa);
+        gather4(fbv + (size_t)(mb.x & 3) * viewStride, mb.x & ~3, s_rec_w[rec + 1], kCp, rowStride, sb);
+        s_stage[ma.y * kLPV + q] = make_float4(sa[0], sa[1], sa[2], sa[3]);
+        s_stage[mb.y * kLPV + q] = make_float4(sb[0], sb[1], sb[2], sb[3]);
+      }
+      if (rec < rec_end) {
+        const int2 ma = s_rec_m[rec];
+        float sa[kCPL];
+        gather4(fbv + (size_t)(ma.x & 3) * viewStride, ma.x & ~3, s_rec_w[rec], kCp, rowStride, sa);
+        s_stage[ma.y * kLPV + q] = make_float4(sa[0], sa[1], sa[2], sa[3]);
+      }
+      __syncthreads();
+    }
+
+    // ---------------- D: d out / d sample_v per voxel (mvn/utils/op.py:147-159 differentiated by hand), in place ----
     float cw[kViewChunk][kCPL];   // conf of this chunk            (conf only)
     float gcw[kViewChunk][kCPL];  // running d conf of this chunk  (conf only)
     if (AGG == kAggConf) {
@@ -173,219 +300,126 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
           gcw[vv][k] = 0.f;
         }
     }
-
 #pragma unroll 1
     for (int r = 0; r < CF::ROUNDS; ++r) {
-      const int run_w = r * NG + warp * kG;  // first of this warp's kG runs
-      // ---------------- A: descriptors + sort keys of this warp's kG*RUN voxels x nv views ----------------
-      for (int it = lane; it < kG * RUN * nv; it += 32) {
-        const int vl = it % (kG * RUN), vv = it / (kG * RUN);
-        const int run = run_w + vl / RUN, j = vl % RUN;
-        const int vi0 = t0 * CF::T0 + run / CF::T1, vi1 = t1 * CF::T1 + run % CF::T1, vz = z0 + j;
-        const int vox = run * RUN + j;
-        int off = -1, kr = 0;
-        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (vi0 < a.N0 && vi1 < a.N1 && vz < a.N2) {
-          const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
-          const float x = __ldg(cp), y = __ldg(cp + 1), z = __ldg(cp + 2);
-          int x0, y0;
-          if (make_taps(x, y, z, s_proj[vv * 3], s_proj[vv * 3 + 1], s_proj[vv * 3 + 2], a.H, a.W, invH, invW,
-                        a.align_corners, x0, y0, w)) {
-            off = ((y0 + 1) * (a.W + 2) + (x0 + 1)) * kCp;
-            const int4 bx = s_box[vv];
-            const int kx = min(max(x0 - bx.x, 0), bx.z - 1), ky = max(y0 - bx.y, 0);
-            const int key = min(ky * bx.z + kx, NB - 1);
-            const int rank = atomicAdd(&s_hist[vv * NB + key], 1);
-            kr = key | (rank << 16);
-          }
-        }
-        s_w[vv * TV + vox] = w;
-        s_off[vv * TV + vox] = off;
-        s_kr[vv * TV + vox] = kr;
-      }
-      __syncwarp();
-
-      // ---------------- B: samples of every view, d out / d sample_v, parked in shared memory ----------------
-      const int run = run_w + g;
+      const int run = r * NG + gid;
       const int i0 = t0 * CF::T0 + run / CF::T1, i1 = t1 * CF::T1 + run % CF::T1;
       const bool run_ok = (i0 < a.N0) && (i1 < a.N1);
-      {
-        // upstream gradient of this lane's 4 channels x RUN voxels, parked in the slots view 0's d will overwrite
-        float go[kCPL][RUN];
-        const float* gp = a.gout + (size_t)b * a.C * a.nvox + ((long long)i0 * a.N1 + i1) * a.N2 + z0;
+      float go[kCPL][RUN];  // upstream gradient of this lane's 4 channels x RUN voxels
+      const float* gp = a.gout + (size_t)b * a.C * a.nvox + ((long long)i0 * a.N1 + i1) * a.N2 + z0;
 #pragma unroll
-        for (int k = 0; k < kCPL; ++k) {
-          const int c = c_lane + k;
-          if (run_ok && c < a.C) {
-            if (RUN == 8) {
-              const f8 tt = ldg256_stream(gp + (size_t)c * a.nvox);
+      for (int k = 0; k < kCPL; ++k) {
+        const int c = c_lane + k;
+        if (run_ok && c < a.C) {
+          if (RUN == 8) {
+            const f8 tt = ldg256_stream(gp + (size_t)c * a.nvox);
 #pragma unroll
-              for (int j = 0; j < RUN; ++j) go[k][j] = tt.v[j];
-            } else {
-              const float4 tt = ldg128_stream(gp + (size_t)c * a.nvox);
-              go[k][0] = tt.x; go[k][1] = tt.y; go[k][2] = tt.z; go[k][3] = tt.w;
-            }
+            for (int j = 0; j < RUN; ++j) go[k][j] = tt.v[j];
           } else {
-#pragma unroll
-            for (int j = 0; j < RUN; ++j) go[k][j] = 0.f;
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < RUN; ++j)
-          s_stage[(run * RUN + j) * kLPV + q] = make_float4(go[0][j], go[1][j], go[2][j], go[3][j]);
-      }
-
-#pragma unroll 2
-      for (int j = 0; j < RUN; ++j) {
-        const int vox = run * RUN + j;
-        const float4 gj = s_stage[vox * kLPV + q];
-        const float go[kCPL] = {gj.x, gj.y, gj.z, gj.w};
-        if (AGG == kAggSum || AGG == kAggConf) {
-#pragma unroll
-          for (int vv = 0; vv < kViewChunk; ++vv) {
-            if (vv < nv) {
-              const int off = s_off[vv * TV + vox];
-              if (off >= 0) {
-                float d[kCPL];
-                if (AGG == kAggConf) {
-                  float s[kCPL];
-                  gather4(fb + (size_t)(v0 + vv) * viewStride, off, s_w[vv * TV + vox], kCp, rowStride, s);
-#pragma unroll
-                  for (int k = 0; k < kCPL; ++k) {
-                    gcw[vv][k] = fmaf(go[k], s[k], gcw[vv][k]);
-                    d[k] = cw[vv][k] * go[k];
-                  }
-                } else {
-#pragma unroll
-                  for (int k = 0; k < kCPL; ++k) d[k] = go[k];
-                }
-                s_stage[(vv * TV + vox) * kLPV + q] = make_float4(d[0], d[1], d[2], d[3]);
-              }
-            }
+            const float4 tt = ldg128_stream(gp + (size_t)c * a.nvox);
+            go[k][0] = tt.x; go[k][1] = tt.y; go[k][2] = tt.z; go[k][3] = tt.w;
           }
         } else {
-          float s[kViewChunk][kCPL];
-          int offs[kViewChunk];
+#pragma unroll
+          for (int j = 0; j < RUN; ++j) go[k][j] = 0.f;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < RUN; ++j) {
+        const int vox = run * RUN + j;
+        float4 s4[kViewChunk];
+        bool ok[kViewChunk];
+#pragma unroll
+        for (int vv = 0; vv < kViewChunk; ++vv) {
+          const float fill = (vv < nv) ? 0.f : kNoView;  // zeroed views take part with 0, absent ones not at all
+          s4[vv] = make_float4(fill, fill, fill, fill);
+          ok[vv] = (vv < nv) && (s_off[vv * TV + vox] >= 0);
+          if (AGG != kAggSum && ok[vv]) s4[vv] = s_stage[(vv * TV + vox) * kLPV + q];
+        }
+        float4 d4[kViewChunk];
+        if (AGG == kAggSum) {
+#pragma unroll
+          for (int vv = 0; vv < kViewChunk; ++vv) d4[vv] = make_float4(go[0][j], go[1][j], go[2][j], go[3][j]);
+        } else if (AGG == kAggConf) {
 #pragma unroll
           for (int vv = 0; vv < kViewChunk; ++vv) {
-            const float fill = (vv < nv) ? 0.f : kNoView;
+            const float sv[kCPL] = {s4[vv].x, s4[vv].y, s4[vv].z, s4[vv].w};
 #pragma unroll
-            for (int k = 0; k < kCPL; ++k) s[vv][k] = fill;
-            offs[vv] = -1;
-            if (vv < nv) {
-              offs[vv] = s_off[vv * TV + vox];
-              if (offs[vv] >= 0)
-                gather4(fb + (size_t)(v0 + vv) * viewStride, offs[vv], s_w[vv * TV + vox], kCp, rowStride, s[vv]);
-            }
+            for (int k = 0; k < kCPL; ++k) gcw[vv][k] = fmaf(go[k][j], sv[k], gcw[vv][k]);  // s == 0 where unseen
+            d4[vv] = make_float4(cw[vv][0] * go[0][j], cw[vv][1] * go[1][j], cw[vv][2] * go[2][j], cw[vv][3] * go[3][j]);
           }
-          float d[kViewChunk][kCPL];
+        } else if (AGG == kAggSoftmax) {
+          // two channels per packed instruction (FFMA2 / FMUL2 / FADD2: each half the same IEEE operation as the
+          // scalar form): d_v = g * e_v / den * (1 - out + s_v), e_v = exp(s_v - max)
+          f2 dl[kViewChunk], dh[kViewChunk];
+          softmax_bwd4_x2(pack2(s4[0].x, s4[0].y), pack2(s4[1].x, s4[1].y), pack2(s4[2].x, s4[2].y),
+                          pack2(s4[3].x, s4[3].y), pack2(go[0][j], go[1][j]), dl);
+          softmax_bwd4_x2(pack2(s4[0].z, s4[0].w), pack2(s4[1].z, s4[1].w), pack2(s4[2].z, s4[2].w),
+                          pack2(s4[3].z, s4[3].w), pack2(go[2][j], go[3][j]), dh);
+#pragma unroll
+          for (int vv = 0; vv < kViewChunk; ++vv) {
+            unpack2(dl[vv], d4[vv].x, d4[vv].y);
+            unpack2(dh[vv], d4[vv].z, d4[vv].w);
+          }
+        } else {
+          float dd[kViewChunk][kCPL];
 #pragma unroll
           for (int k = 0; k < kCPL; ++k) {
-            float m = s[0][k];
+            const float sk[kViewChunk] = {(&s4[0].x)[k], (&s4[1].x)[k], (&s4[2].x)[k], (&s4[3].x)[k]};
+            float m = sk[0];
             int am = 0;
 #pragma unroll
             for (int vv = 1; vv < kViewChunk; ++vv)
-              if (s[vv][k] > m) { m = s[vv][k]; am = vv; }
-            if (AGG == kAggSoftmax) {
-              float e[kViewChunk], den = 0.f, num = 0.f;
+              if (sk[vv] > m) { m = sk[vv]; am = vv; }
 #pragma unroll
-              for (int vv = 0; vv < kViewChunk; ++vv) {
-                e[vv] = fast_ex2((s[vv][k] - m) * kLog2eF);
-                den += e[vv];
-                num = fmaf(s[vv][k], e[vv], num);
-              }
-              const float inv = fast_rcp(den);
-              const float o1 = 1.f - num * inv;  // 1 - out
-              const float gi = go[k] * inv;
-#pragma unroll
-              for (int vv = 0; vv < kViewChunk; ++vv) d[vv][k] = gi * e[vv] * (o1 + s[vv][k]);
-            } else {
-#pragma unroll
-              for (int vv = 0; vv < kViewChunk; ++vv) d[vv][k] = (vv == am) ? go[k] : 0.f;
-            }
+            for (int vv = 0; vv < kViewChunk; ++vv) dd[vv][k] = (vv == am) ? go[k][j] : 0.f;
           }
 #pragma unroll
-          for (int vv = 0; vv < kViewChunk; ++vv)
-            if (vv < nv && offs[vv] >= 0)
-              s_stage[(vv * TV + vox) * kLPV + q] = make_float4(d[vv][0], d[vv][1], d[vv][2], d[vv][3]);
+          for (int vv = 0; vv < kViewChunk; ++vv) d4[vv] = make_float4(dd[vv][0], dd[vv][1], dd[vv][2], dd[vv][3]);
         }
-      }
-    }
-    __syncthreads();
-
-    // ---------------- S: exclusive scan of each view's histogram (warp vv), then the sorted index lists ----------------
-    if (warp < nv) {
-      int* h = s_hist + warp * NB;
-      int carry = 0;
-#pragma unroll 4
-      for (int i = 0; i < NB / 32; ++i) {
-        const int v = h[i * 32 + lane];
-        int incl = v;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int n = __shfl_up_sync(0xffffffffu, incl, o);
-          if (lane >= o) incl += n;
-        }
-        h[i * 32 + lane] = carry + incl - v;
-        carry += __shfl_sync(0xffffffffu, incl, 31);
-      }
-      if (lane == 0) s_n[warp] = carry;
-    }
-    __syncthreads();
-    for (int it = tid; it < nv * TV; it += NT) {
-      const int off = s_off[it];
-      if (off >= 0) {
-        const int vv = it / TV, vox = it % TV, kr = s_kr[it];
-        const int pos = s_hist[vv * NB + (kr & 0xffff)] + (kr >> 16);
-        s_idx[vv * TV + pos] = (unsigned short)vox;
+        for (int vv = 0; vv < kViewChunk; ++vv)
+          if (ok[vv]) s_stage[(vv * TV + vox) * kLPV + q] = d4[vv];
       }
     }
-    // record r of the concatenated sorted lists belongs to view #(i in 1..3 : r >= b_i)
-    const int b1 = s_n[0], b2 = b1 + (nv > 1 ? s_n[1] : 0), b3 = b2 + (nv > 2 ? s_n[2] : 0);
-    const int n_total = b3 + (nv > 3 ? s_n[3] : 0);
     __syncthreads();
 
     // ---------------- C: row walk over the cell-sorted records ----------------
     {
-      const int chunk = (n_total + NG - 1) / NG;
-      const int gid = warp * kG + g;
-      int rec = gid * chunk;
-      const int rec_end = min(n_total, rec + chunk);
       float4 a00 = make_float4(0.f, 0.f, 0.f, 0.f), a01 = a00, a10 = a00, a11 = a00;
-      int cur = -1, cur_v = 0;
-      float* gv = gb;
-      for (; rec < rec_end; ++rec) {
-        const int vv = (rec >= b1) + (rec >= b2) + (rec >= b3);
-        const int vox = s_idx[vv * TV + rec - (vv == 0 ? 0 : (vv == 1 ? b1 : (vv == 2 ? b2 : b3)))];
-        const int off = s_off[vv * TV + vox];
-        const float4 w = s_w[vv * TV + vox];
-        const float4 d = s_stage[(vv * TV + vox) * kLPV + q];
-        if (off != cur || vv != cur_v) {
-          const bool shift = (vv == cur_v) && (off == cur + kCp);
+      int cur = -64;      // (offset | view) of the cell in the registers; -64 = none (never one cell left of anything)
+      float* pc = gbv;    // its north-west texel in the gradient map
+#pragma unroll 1
+      for (int rec = rec_begin; rec < rec_end; ++rec) {
+        const int2 m = s_rec_m[rec];
+        const float4 w = s_rec_w[rec];
+        const float4 d = s_stage[m.y * kLPV + q];
+        if (m.x != cur) {
+          const bool shift = (m.x == cur + kCp);  // same view (low bits), next cell to the right in the same row
           if (cur >= 0) {
-            red4(gv + cur, a00);
-            red4(gv + cur + rowStride, a10);
+            red4(pc, a00);
+            red4(pc + rowStride, a10);
             if (!shift) {
-              red4(gv + cur + kCp, a01);
-              red4(gv + cur + rowStride + kCp, a11);
+              red4(pc + kCp, a01);
+              red4(pc + rowStride + kCp, a11);
             }
           }
-          if (shift && cur >= 0) {
+          if (shift) {
             a00 = a01; a10 = a11;
           } else {
             a00 = make_float4(0.f, 0.f, 0.f, 0.f); a10 = a00;
           }
           a01 = make_float4(0.f, 0.f, 0.f, 0.f); a11 = a01;
-          cur = off; cur_v = vv;
-          gv = gb + (size_t)(v0 + vv) * viewStride;
+          cur = m.x;
+          pc = gbv + (size_t)(m.x & 3) * viewStride + (m.x & ~3);
         }
         fma4(a00, w.x, d); fma4(a01, w.y, d); fma4(a10, w.z, d); fma4(a11, w.w, d);
       }
       if (cur >= 0) {
-        red4(gv + cur, a00);
-        red4(gv + cur + kCp, a01);
-        red4(gv + cur + rowStride, a10);
-        red4(gv + cur + rowStride + kCp, a11);
+        red4(pc, a00);
+        red4(pc + kCp, a01);
+        red4(pc + rowStride, a10);
+        red4(pc + rowStride + kCp, a11);
       }
     }
 
@@ -487,8 +521,11 @@ cudaError_t launch_agg(UnprojArgs& a, const UnprojShape& s, cudaStream_t st) {
 }  // namespace
 
 bool unproject_bwd_tile_eligible(const UnprojShape& s, const float* grad_out) {
+  // MEASURED (profiles/r2a_k1bwd_tile_ncu.txt): at cfg3 this formulation cuts the L2 reduction sectors 2.5x but runs
+  // 1.37 ms against 1.05 ms for the scatter kernel (issue-bound: 2.6 k instructions per warp at 16 warps per SM), so it
+  // is opt-in: LT_B200_K1BWD=tile.
   const char* e = getenv("LT_B200_K1BWD");
-  if (e && e[0] == 's') return false;  // "scatter"
+  if (!(e && e[0] == 't')) return false;
   if (padded_channels(s.C) != kCp) return false;
   if (s.N2 % 8 != 0 || (reinterpret_cast<uintptr_t>(grad_out) & 31u) != 0) return false;
   if ((s.agg == kAggMax || s.agg == kAggSoftmax) && s.V > kViewChunk) return false;

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(kCeThreads) k_ce_argmin(const float* __restric
   // thread t owns voxels base + t*8 .. +7 (24 consecutive floats)
   float cx[kCeEpt], cy[kCeEpt], cz[kCeEpt];
   const long long v0 = base + (long long)threadIdx.x * kCeEpt;
-  if ((nvox & 3) == 0 && v0 + kCeEpt <= nvox) {  // 96 consecutive, 16-byte aligned bytes
+  if ((nvox & 3) == 0 && (reinterpret_cast<uintptr_t>(coord) & 15u) == 0 && v0 + kCeEpt <= nvox) {  // 96 consecutive, 16-byte aligned bytes
     float f[kCeEpt * 3];
     const float4* p4 = reinterpret_cast<const float4*>(cb + v0 * 3);
 #pragma unroll

@@ -122,7 +122,7 @@ class _SoftArgmaxWithCE(torch.autograd.Function):
         with torch.cuda.device(prob.device):
             st, dev = _stream(), prob.device
             gvol = torch.empty_like(prob)
-            gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 3), device=dev)
+            gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 3), device=dev, dtype=torch.float32)
             gp = _f32c(g_prob) if g_prob is not None else None
             vals = dots = None
             if g_loss is not None:

@@ -45,16 +45,16 @@ def _stream():
 
 # ---- tensors that already live in the gather layout -----------------------------------------------------------------
 # triangulation.process_features writes K1's gather layout "hwcp" directly and returns a strided (B*V,C,H,W) view of its
-# interior; K1's backward hands its gradient map back the same way. Such buffers are remembered by the address and size of
-# their storage; a tensor is taken as "already hwcp" only if its storage is one of them AND its strides/offset are exactly
-# the interior view (also after the `.view(batch_size, n_views, ...)` of triangulation.py:346). Anything else takes K0.
-_HWCP = {}  # storage address -> (kind, number of floats); kind 'feat' has a zero border, 'grad' has a scratch border
+# interior; K1's backward hands its gradient map back the same way. The fact "this storage holds a hwcp buffer" is an
+# attribute ON THE STORAGE OBJECT (torch keeps one python object per live storage, shared by every view / detach() of
+# it), so it disappears with the buffer: no registry, no addresses, nothing to prune, nothing shared between threads.
+# A tensor is taken as "already hwcp" only if its storage carries the tag AND its strides/offset are exactly the interior
+# view (also after the `.view(batch_size, n_views, ...)` of triangulation.py:346). Anything else takes K0.
+_HWCP_ATTR = "_lt_b200_hwcp"  # -> (kind, number of floats); kind 'feat' has a zero border, 'grad' a scratch border
 
 
 def _hwcp_register(base, kind):
-    if len(_HWCP) > 4096:
-        _HWCP.clear()
-    _HWCP[base.untyped_storage().data_ptr()] = (kind, base.numel())
+    setattr(base.untyped_storage(), _HWCP_ATTR, (kind, base.numel()))
 
 
 def _hwcp_view(base, lead, C, H, W):
@@ -73,7 +73,7 @@ def _hwcp_base(t, kind):
     if t.dtype != torch.float32 or not t.is_cuda or t.dim() < 4 or t.numel() == 0:
         return None
     st = t.untyped_storage()
-    entry = _HWCP.get(st.data_ptr())
+    entry = getattr(st, _HWCP_ATTR, None)
     if entry is None or entry[0] != kind:
         return None
     *lead, C, H, W = t.shape
@@ -228,7 +228,8 @@ class _SoftArgmax(torch.autograd.Function):
             gvol = torch.empty_like(prob)
             if nvox == 0 or B * J == 0:
                 return gvol.to(dtype), None, None, None
-            gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 3), device=prob.device)
+            gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 3), device=prob.device,
+                                                                          dtype=torch.float32)
             gp = _f32c(g_prob) if g_prob is not None else None
             dots = None
             if gp is not None and softmax:
@@ -320,7 +321,8 @@ class _SoftArgmax2D(torch.autograd.Function):
         with torch.cuda.device(prob.device):
             ghm = torch.empty_like(prob)
             if B * J * H * W > 0:
-                gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 2), device=prob.device)
+                gc = _f32c(g_coords) if g_coords is not None else torch.zeros((B, J, 2), device=prob.device,
+                                                                              dtype=torch.float32)
                 gp = _f32c(g_prob) if g_prob is not None else None
                 _lib.check(L.lt_softargmax2d_bwd(_lib.ptr(prob), _lib.ptr(coords), _lib.ptr(gc), _lib.ptr(gp),
                                                  _lib.ptr(ghm), B * J, H, W, softmax, multiplier, _stream()))
