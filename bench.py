@@ -8,7 +8,7 @@ One "step" = one pass of the hot path over one batch: K0 (layout) + K1 fwd + K2 
 `value`  : device-resident arm, direct C-ABI launches on preallocated buffers, CUDA events, max over ranks.
 `e2e`    : the public python API (lt_b200.unproject_heatmaps / integrate_tensor_3d_with_coordinates under autograd) fed
            from PINNED HOST tensors every step (H2D inside the timed region: feature maps, projection matrices and the
-           cuboid specs; the coordinate volumes are built on the device like the reference does) with the loss +
+           cuboid specs; the voxel coordinates are evaluated from the specs inside the kernels, lt_b200.CoordSpec) with the loss +
            coordinates read back.
 `roofline`: per-kernel CUDA-event durations taken inside the same timed loop against MEASURED_PEAKS.json.
 `cpu_baseline`: the oracle port of the reference's torch CPU path, timed on this box's host cores (rank 0, N=1).
@@ -225,13 +225,13 @@ def _valid_voxel_views(coord, proj, H, W):
 
 
 class E2EStep:
-    """Public-API arm: pinned host inputs -> H2D -> coordinate volumes -> unproject (+ its backward) and soft-argmax
+    """Public-API arm: pinned host inputs -> H2D -> unproject (+ its backward) and soft-argmax
     -> L1 loss (+ its backward) -> loss + coordinates back to the host. The same work as one step of the device arm.
 
     The host inputs are what the reference's forward receives from its data loader: feature maps, projection
     matrices and the cuboid of every item (base point, side, rotation: 18 floats). Like the reference
-    (triangulation.py:280-341 builds `coord_volumes` on the device), the coordinate volumes are made on the device
-    every step (lt_b200.volumetric.coord_volumes_from_specs), not shipped over PCIe.
+    (triangulation.py:280-341 builds `coord_volumes` on the device), nothing per voxel is shipped over PCIe: the ops get
+    a lt_b200.CoordSpec and evaluate the voxel centres in-kernel (bit-identical to building the tensor with K6).
 
     Every step copies ITS OWN inputs from pinned host memory inside the timed region. Like a DataLoader with
     pin_memory + non_blocking prefetch, the copy of step i+1 is issued on a second stream while step i computes
@@ -295,7 +295,9 @@ class E2EStep:
         import lt_b200
         w, d = self.w, self.dbuf[k]
         feat = d["feat"].detach().requires_grad_(True)
-        coord = lt_b200.volumetric.coord_volumes_from_specs(d["spec"], self.vol_size)
+        # the cuboids travel as 18 floats per item; K1 / K2 evaluate the voxel centres from them in-kernel (lt_b200.CoordSpec,
+        # bit-identical to building the reference's coord_volumes tensor with K6 and reading it back four times)
+        coord = lt_b200.CoordSpec(d["spec"], self.vol_size)
         vol = lt_b200.unproject_heatmaps(feat, d["proj"], coord, w["agg"], d.get("conf"))
         # The V2V net between the two ops stays in PyTorch and is out of scope: as in the device arm and the CPU arm,
         # its output (x) and the gradient it sends back into the unprojected volume (gvol) are device-resident tensors.
@@ -682,9 +684,9 @@ def main():
                "note": "public python ops under autograd (captured once into a CUDA graph per input set when cuda_graph is "
                        "true, replayed every step); pinned-host inputs (feature maps, projection matrices, "
                        "18-float cuboid specs) staged in ONE pinned buffer and copied every step with one cudaMemcpyAsync on a "
-                       "second stream (prefetch depth 2), coordinate "
-                       "volumes built on the device as triangulation.py:280-341 does, loss + coordinates read back "
-                       "every step"}
+                       "second stream (prefetch depth 2), voxel "
+                       "coordinates evaluated inside K1/K2 from the specs (the reference builds the coordinate volumes "
+                       "on the device too, triangulation.py:280-341), loss + coordinates read back every step"}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

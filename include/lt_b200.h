@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define LT_ABI_VERSION 1
+#define LT_ABI_VERSION 2   /* 2: + the *_spec entry points (coordinates computed in the consuming kernel) */
 #define LT_ERR_INVALID (-1)
 
 /* view aggregation, op.py:147-161 (`conf` covers every method name starting with "conf") */
@@ -140,6 +140,28 @@ int lt_softargmax2d_bwd(const float *prob, const float *coords, const float *gra
 #define LT_COORD_SPEC 18
 int lt_coord_volumes(const float *spec, float *out, int B, int N0, int N1, int N2, int transfer,
                      void *stream);
+
+/* ---- K1 / K2 with the coordinates computed IN the kernel   ------------------------------------
+ * The reference builds coord_volumes in python (triangulation.py:280-341) and every op reads 12 bytes per voxel of it.
+ * These variants take the K6 spec (B, LT_COORD_SPEC) + `transfer` INSTEAD of the coordinate tensor and evaluate the same
+ * fp32 arithmetic per voxel (one definition, shared with lt_coord_volumes): outputs are bit-identical to running the
+ * tensor variants on lt_coord_volumes' output.  The volume extents are explicit (K2's tensor variants only need nvox):
+ * nvox = N0*N1*N2 <= 2^31-1, transfer needs N1 == N2.  Everything else as documented for the tensor variants. */
+int lt_unproject_fwd_spec(const float *feat_hwc, const float *proj, const float *coord_spec, int transfer,
+                          const float *conf, float *out, int B, int V, int C, int H, int W, int N0, int N1, int N2,
+                          int agg, int align_corners, void *stream);
+int lt_unproject_bwd_spec(const float *grad_out, const float *feat_hwc, const float *proj, const float *coord_spec,
+                          int transfer, const float *conf, float *grad_feat_hwc, float *grad_conf, void *conf_ws,
+                          int B, int V, int C, int H, int W, int N0, int N1, int N2, int agg, int align_corners,
+                          void *stream);
+int lt_softargmax_partial_spec(const float *vol, const float *coord_spec, int transfer, float *stats, void *ws, int B,
+                               int J, int N0, int N1, int N2, int softmax, float multiplier, void *stream);
+int lt_softargmax_fwd_spec(const float *vol, const float *coord_spec, int transfer, float *coords, float *prob,
+                           float *stats, void *ws, int B, int J, int N0, int N1, int N2, int softmax,
+                           float multiplier, void *stream);
+int lt_softargmax_bwd_spec(const float *prob, const float *coord_spec, int transfer, const float *coords,
+                           const float *grad_coords, const float *grad_prob, const float *dots, float *grad_vol,
+                           int B, int J, int N0, int N1, int N2, int softmax, float multiplier, void *stream);
 
 /* ---- K5: volumetric cross-entropy loss  (mvn/models/loss.py:52-80 VolumetricCELoss) --------------
  * coord (B,nvox,3)  prob (B,J,nvox) = second output of lt_softargmax_fwd  kp_gt (B,J,3)  validity (B,J)

@@ -38,6 +38,11 @@ SIGNATURES = {
     "lt_softargmax_merge": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "lt_softargmax_bwd_dot": (_i, [_vp, _vp, _vp, _vp, _i, _i, _ll, _vp]),
     "lt_softargmax_bwd": (_i, [_vp] * 7 + [_i, _i, _ll, _i, _f, _vp]),
+    "lt_unproject_fwd_spec": (_i, [_vp, _vp, _vp, _i, _vp, _vp] + [_i] * 10 + [_vp]),
+    "lt_unproject_bwd_spec": (_i, [_vp] * 4 + [_i] + [_vp] * 4 + [_i] * 10 + [_vp]),
+    "lt_softargmax_partial_spec": (_i, [_vp, _vp, _i, _vp, _vp] + [_i] * 6 + [_f, _vp]),
+    "lt_softargmax_fwd_spec": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp] + [_i] * 6 + [_f, _vp]),
+    "lt_softargmax_bwd_spec": (_i, [_vp, _vp, _i] + [_vp] * 5 + [_i] * 6 + [_f, _vp]),
     "lt_softargmax2d_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _f, _vp]),
     "lt_softargmax2d_bwd": (_i, [_vp] * 5 + [_i, _i, _i, _i, _f, _vp]),
     "lt_coord_volumes": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
@@ -87,7 +92,7 @@ def lib():
             fn = getattr(handle, name)  # AttributeError here = header/library mismatch
             fn.restype = res
             fn.argtypes = args
-        if handle.lt_abi_version() != 1:
+        if handle.lt_abi_version() != 2:
             raise RuntimeError("lt_b200: ABI version mismatch")
         _lib = handle
     return _lib

@@ -196,6 +196,83 @@ LT_API int lt_coord_volumes(const float* spec, float* out, int B, int N0, int N1
   return finish(__func__, lt::launch_coord_volumes(spec, out, B, N0, N1, N2, transfer ? 1 : 0, as_stream(stream)));
 }
 
+// ---- the same ops with the coordinates computed in the kernel from the K6 spec (coordspec.cuh) ----
+static bool bad_spec_volume(int N0, int N1, int N2, int transfer) {
+  return N0 < 0 || N1 < 0 || N2 < 0 || (long long)N0 * N1 * N2 > 0x7fffffffLL || (transfer && N1 != N2);
+}
+
+LT_API int lt_unproject_fwd_spec(const float* feat_hwc, const float* proj, const float* coord_spec, int transfer,
+                          const float* conf, float* out, int B, int V, int C, int H, int W, int N0, int N1, int N2,
+                          int agg, int align_corners, void* stream) {
+  LT_REQUIRE(!bad_unproj_shape(B, V, C, H, W, N0, N1, N2), "bad shape");
+  LT_REQUIRE(!bad_spec_volume(N0, N1, N2, transfer), "more than 2^31 voxels per item, or transfer with N1 != N2");
+  LT_REQUIRE(agg >= LT_AGG_SUM && agg <= LT_AGG_SOFTMAX, "unknown aggregation");
+  if ((long long)B * C * N0 * N1 * N2 == 0) return 0;
+  LT_REQUIRE(feat_hwc && proj && coord_spec && out, "null pointer");
+  LT_REQUIRE(al16(feat_hwc) && al16(proj), "feat_hwc and proj must be 16-byte aligned");
+  LT_REQUIRE(agg != LT_AGG_CONF || conf, "conf aggregation needs vol_confidences");
+  lt::UnprojShape s{B, V, C, H, W, N0, N1, N2, agg, align_corners ? 1 : 0};
+  const lt::CoordSpecArg cs{coord_spec, N1, N2, transfer ? 1 : 0};
+  return finish(__func__, lt::launch_unproject_fwd(feat_hwc, proj, nullptr, conf, out, s, as_stream(stream), &cs));
+}
+
+LT_API int lt_unproject_bwd_spec(const float* grad_out, const float* feat_hwc, const float* proj, const float* coord_spec,
+                          int transfer, const float* conf, float* grad_feat_hwc, float* grad_conf, void* conf_ws,
+                          int B, int V, int C, int H, int W, int N0, int N1, int N2, int agg, int align_corners,
+                          void* stream) {
+  LT_REQUIRE(!bad_unproj_shape(B, V, C, H, W, N0, N1, N2), "bad shape");
+  LT_REQUIRE(!bad_spec_volume(N0, N1, N2, transfer), "more than 2^31 voxels per item, or transfer with N1 != N2");
+  LT_REQUIRE(agg >= LT_AGG_SUM && agg <= LT_AGG_SOFTMAX, "unknown aggregation");
+  if ((long long)B * C == 0) return 0;
+  LT_REQUIRE(feat_hwc && proj && coord_spec && grad_feat_hwc, "null pointer");
+  LT_REQUIRE(al16(feat_hwc) && al16(proj) && al16(grad_feat_hwc) && al16(conf_ws),
+             "feat_hwc, proj, grad_feat_hwc and conf_ws must be 16-byte aligned");
+  LT_REQUIRE((long long)N0 * N1 * N2 == 0 || grad_out, "null grad_out");
+  LT_REQUIRE(agg != LT_AGG_CONF || conf, "conf aggregation needs vol_confidences");
+  LT_REQUIRE(!(agg == LT_AGG_CONF && grad_conf) || conf_ws, "grad_conf needs conf_ws");
+  lt::UnprojShape s{B, V, C, H, W, N0, N1, N2, agg, align_corners ? 1 : 0};
+  const lt::CoordSpecArg cs{coord_spec, N1, N2, transfer ? 1 : 0};
+  return finish(__func__, lt::launch_unproject_bwd(grad_out, feat_hwc, proj, nullptr, conf, grad_feat_hwc, grad_conf,
+                                                   conf_ws, s, as_stream(stream), &cs));
+}
+
+LT_API int lt_softargmax_partial_spec(const float* vol, const float* coord_spec, int transfer, float* stats, void* ws,
+                               int B, int J, int N0, int N1, int N2, int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0, "negative extent");
+  LT_REQUIRE(!bad_spec_volume(N0, N1, N2, transfer), "more than 2^31 voxels per item, or transfer with N1 != N2");
+  LT_REQUIRE(B <= 65535, "B > 65535");
+  LT_REQUIRE(multiplier > 0.f, "multiplier must be > 0 (scale on the caller side otherwise)");
+  if (B * J == 0) return 0;
+  const long long nvox = (long long)N0 * N1 * N2;
+  LT_REQUIRE(stats && (nvox == 0 || (vol && coord_spec && ws)), "null pointer");
+  const lt::CoordSpecArg cs{coord_spec, N1, N2, transfer ? 1 : 0};
+  return finish(__func__, lt::launch_softargmax_partial(vol, nullptr, stats, ws, B, J, nvox, softmax ? 1 : 0,
+                                                        multiplier, as_stream(stream), &cs));
+}
+
+LT_API int lt_softargmax_fwd_spec(const float* vol, const float* coord_spec, int transfer, float* coords, float* prob,
+                           float* stats, void* ws, int B, int J, int N0, int N1, int N2, int softmax,
+                           float multiplier, void* stream) {
+  int rc = lt_softargmax_partial_spec(vol, coord_spec, transfer, stats, ws, B, J, N0, N1, N2, softmax, multiplier, stream);
+  if (rc) return rc;
+  return lt_softargmax_finalize(vol, stats, coords, prob, B, J, (long long)N0 * N1 * N2, softmax, multiplier, stream);
+}
+
+LT_API int lt_softargmax_bwd_spec(const float* prob, const float* coord_spec, int transfer, const float* coords,
+                           const float* grad_coords, const float* grad_prob, const float* dots, float* grad_vol,
+                           int B, int J, int N0, int N1, int N2, int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0, "negative extent");
+  LT_REQUIRE(!bad_spec_volume(N0, N1, N2, transfer), "more than 2^31 voxels per item, or transfer with N1 != N2");
+  LT_REQUIRE(B <= 65535, "B > 65535");
+  const long long nvox = (long long)N0 * N1 * N2;
+  if ((long long)B * J * nvox == 0) return 0;
+  LT_REQUIRE(prob && coord_spec && coords && grad_coords && grad_vol, "null pointer");
+  LT_REQUIRE(!(softmax && grad_prob) || dots, "grad_prob given without dots");
+  const lt::CoordSpecArg cs{coord_spec, N1, N2, transfer ? 1 : 0};
+  return finish(__func__, lt::launch_softargmax_bwd(prob, nullptr, coords, grad_coords, grad_prob, dots, grad_vol, B, J,
+                                                    nvox, softmax ? 1 : 0, multiplier, as_stream(stream), &cs));
+}
+
 LT_API size_t lt_volce_ws_bytes(int B, int J, long long nvox) { return lt::volce_ws_bytes(B, J, nvox); }
 
 LT_API int lt_volce_fwd(const float* coord, const float* prob, const float* kp_gt, const float* validity, float* loss,

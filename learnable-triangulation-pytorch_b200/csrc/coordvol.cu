@@ -11,26 +11,10 @@
 // transfer (triangulation.py:336-339): out[i0,i1,i2] = cv[i0, i2, N1-1-i1] (permute(0,2,1,3), then reverse axis 1).
 // Pure streaming write: 12 bytes per voxel.
 #include "common.cuh"
+#include "coordspec.cuh"
 #include "kernels.h"
 
 namespace lt {
-
-// spec per item: pos[3] step[3] centre[3] rot[9] (row-major) = 18 floats
-constexpr int kCoordSpec = 18;
-
-__device__ __forceinline__ void coord_of(const float* __restrict__ s, int i0, int i1, int i2, float (&o)[3]) {
-  const float g0 = __fadd_rn(s[0], __fmul_rn(s[3], (float)i0));
-  const float g1 = __fadd_rn(s[1], __fmul_rn(s[4], (float)i1));
-  const float g2 = __fadd_rn(s[2], __fmul_rn(s[5], (float)i2));
-  const float d0 = __fsub_rn(g0, s[6]), d1 = __fsub_rn(g1, s[7]), d2 = __fsub_rn(g2, s[8]);
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    float acc = __fmul_rn(s[9 + 3 * k], d0);
-    acc = __fmaf_rn(s[10 + 3 * k], d1, acc);
-    acc = __fmaf_rn(s[11 + 3 * k], d2, acc);
-    o[k] = __fadd_rn(acc, s[6 + k]);
-  }
-}
 
 // one thread = 4 consecutive voxels along the last axis = 12 consecutive floats = three 16-byte stores
 __global__ void __launch_bounds__(256) k_coord_volume(const float* __restrict__ spec, float* __restrict__ out, int N0,

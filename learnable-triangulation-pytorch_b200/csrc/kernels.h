@@ -12,15 +12,24 @@ size_t feat_layout_elems(int BV, int C, int H, int W);
 cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwcp,
                                cudaStream_t st);
 
+// coordinates computed in the consuming kernel from the per-item 18-float spec of K6 instead of read from the tensor
+// (coordspec.cuh); N1, N2 = the two inner volume extents, transfer = the CMU -> Human3.6M axis swap
+struct CoordSpecArg {
+  const float* spec;  // (B, 18) device pointer
+  int N1, N2, transfer;
+};
+
 struct UnprojShape {
   int B, V, C, H, W, N0, N1, N2, agg, align_corners;
 };
 cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const float* coord,
-                                 const float* conf, float* out, const UnprojShape& s, cudaStream_t st);
+                                 const float* conf, float* out, const UnprojShape& s, cudaStream_t st,
+                                 const CoordSpecArg* spec = nullptr);
 size_t unproject_bwd_ws_bytes(int B, int V, int C, int N0, int N1, int N2);
 cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, const float* proj,
                                  const float* coord, const float* conf, float* grad_feat_hwc,
-                                 float* grad_conf, void* conf_ws, const UnprojShape& s, cudaStream_t st);
+                                 float* grad_conf, void* conf_ws, const UnprojShape& s, cudaStream_t st,
+                                 const CoordSpecArg* spec = nullptr);
 
 // on-chip merged formulation of the backward (unproject_bwd_tile.cu); UnprojArgs lives in unproject.cuh
 struct UnprojArgs;
@@ -30,7 +39,8 @@ cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float
 
 size_t softargmax_ws_bytes(int B, int J, long long nvox);
 cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,
-                                      int J, long long nvox, int softmax, float mult, cudaStream_t st);
+                                      int J, long long nvox, int softmax, float mult, cudaStream_t st,
+                                      const CoordSpecArg* spec = nullptr);
 cudaError_t launch_softargmax_finalize(const float* vol, const float* stats, float* coords, float* prob,
                                        int B, int J, long long nvox, int softmax, float mult,
                                        cudaStream_t st);
@@ -41,7 +51,7 @@ cudaError_t launch_softargmax_bwd_dot(const float* prob, const float* grad_prob,
 cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const float* coords,
                                   const float* grad_coords, const float* grad_prob, const float* dots,
                                   float* grad_vol, int B, int J, long long nvox, int softmax, float mult,
-                                  cudaStream_t st);
+                                  cudaStream_t st, const CoordSpecArg* spec = nullptr);
 
 cudaError_t launch_coord_volumes(const float* spec, float* out, int B, int N0, int N1, int N2, int transfer,
                                  cudaStream_t st);

@@ -14,6 +14,7 @@
 // exp is evaluated as ex2(fma(x, mult*log2e, -m*log2e)): one FFMA + one MUFU per element; the shift is
 // common to numerator and denominator so only the rounding of log2e (3e-8 * |x-m|) enters the result.
 #include "common.cuh"
+#include "coordspec.cuh"
 #include "kernels.h"
 
 namespace lt {
@@ -32,27 +33,34 @@ __device__ __forceinline__ float ex2_approx(float x) {
 
 static inline int sam_chunks(long long nvox) { return (int)((nvox + kSamChunk - 1) / kSamChunk); }
 
-// ---------------------------------------------------------------------------------------------------
-// pass 1: partial tuples. ws layout: [(b*J + j)][chunk*kSamWarps + warp][5]
-// VEC: nvox % 4 == 0 (rows 16-byte aligned) -> 128-bit loads.
-template <bool VEC, bool SOFTMAX>
-__global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __restrict__ vol,
-                                                           const float* __restrict__ coord,
-                                                           float* __restrict__ ws, int J, long long nvox,
-                                                           float mult) {
-  const int b = blockIdx.y, chunk = blockIdx.x, nchunk = gridDim.x;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long base = (long long)chunk * kSamChunk;
-  const float* cb = coord + (size_t)b * nvox * 3;
-
-  // coordinates of this thread's 16 voxels: group i covers voxels base + (i*256 + tid)*4 .. +3
-  float cx[kSamEpt], cy[kSamEpt], cz[kSamEpt];
-  bool ok[kSamEpt / 4];
+// xyz of this thread's 16 voxels: group i covers voxels base + (i*256 + tid)*4 .. +3. Either read from the coordinate
+// volume (128-bit loads when VEC) or evaluated from the item's 18-float spec (coordspec.cuh): same values bit for bit.
+template <bool VEC>
+__device__ __forceinline__ void load_xyz16(const CoordSrc& cs, const float* s_spec, int b, long long base, long long nvox,
+                                           float (&cx)[kSamEpt], float (&cy)[kSamEpt], float (&cz)[kSamEpt]) {
+  if (cs.spec != nullptr) {
+#pragma unroll
+    for (int i = 0; i < kSamEpt / 4; ++i) {
+      const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+      unsigned t = (unsigned)v0;               // nvox < 2^31 in spec mode (checked by the ABI)
+      int i2 = (int)(t % (unsigned)cs.N2);
+      t /= (unsigned)cs.N2;
+      int i1 = (int)(t % (unsigned)cs.N1), i0 = (int)(t / (unsigned)cs.N1);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float o[3] = {0.f, 0.f, 0.f};
+        if (v0 + e < nvox) coord_of_voxel(s_spec, cs.transfer, cs.N1, i0, i1, i2, o);
+        cx[i * 4 + e] = o[0]; cy[i * 4 + e] = o[1]; cz[i * 4 + e] = o[2];
+        if (++i2 == cs.N2) { i2 = 0; if (++i1 == cs.N1) { i1 = 0; ++i0; } }
+      }
+    }
+    return;
+  }
+  const float* cb = cs.coord + (size_t)b * nvox * 3;
 #pragma unroll
   for (int i = 0; i < kSamEpt / 4; ++i) {
     const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
-    ok[i] = VEC && (v0 < nvox);  // rows are only 16-byte aligned when nvox % 4 == 0
-    if (ok[i]) {
+    if (VEC && v0 < nvox) {  // rows are only 16-byte aligned when nvox % 4 == 0
       const float4* p = reinterpret_cast<const float4*>(cb + v0 * 3);
       float4 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
       cx[i * 4 + 0] = a.x;  cy[i * 4 + 0] = a.y;  cz[i * 4 + 0] = a.z;
@@ -70,6 +78,35 @@ __global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __res
       }
     }
   }
+}
+// the item's spec -> shared memory (no-op in tensor mode); every thread of the CTA must call it
+__device__ __forceinline__ void stage_spec(const CoordSrc& cs, int b, float* s_spec) {
+  if (cs.spec != nullptr) {
+    if (threadIdx.x < kCoordSpec) s_spec[threadIdx.x] = __ldg(cs.spec + (size_t)b * kCoordSpec + threadIdx.x);
+    __syncthreads();
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// pass 1: partial tuples. ws layout: [(b*J + j)][chunk*kSamWarps + warp][5]
+// VEC: nvox % 4 == 0 (rows 16-byte aligned) -> 128-bit loads.
+template <bool VEC, bool SOFTMAX>
+__global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __restrict__ vol, const CoordSrc cs,
+                                                           float* __restrict__ ws, int J, long long nvox,
+                                                           float mult) {
+  __shared__ float s_spec[kCoordSpec];
+  const int b = blockIdx.y, chunk = blockIdx.x, nchunk = gridDim.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long base = (long long)chunk * kSamChunk;
+  stage_spec(cs, b, s_spec);
+
+  float cx[kSamEpt], cy[kSamEpt], cz[kSamEpt];
+  bool ok[kSamEpt / 4];
+#pragma unroll
+  for (int i = 0; i < kSamEpt / 4; ++i)
+    ok[i] = VEC && (base + ((long long)i * kSamThreads + threadIdx.x) * 4 < nvox);
+  load_xyz16<VEC>(cs, s_spec, b, base, nvox, cx, cy, cz);
 
   const float L = mult * kLog2e;
   // rows are double-buffered in registers: the loads of joint j+1 are in flight while joint j is reduced
@@ -233,37 +270,18 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_final(const float* __restri
 // grid (chunk, b): coordinates in registers, loop over joints (same reuse as k_sam_stats).
 template <bool VEC, bool SOFTMAX, bool HAS_GP>
 __global__ void __launch_bounds__(kSamThreads) k_sam_bwd(const float* __restrict__ prob,
-                                                         const float* __restrict__ coord,
+                                                         const CoordSrc cs,
                                                          const float* __restrict__ coords_out,
                                                          const float* __restrict__ gcoords,
                                                          const float* __restrict__ gprob,
                                                          const float* __restrict__ dots, float* __restrict__ gvol,
                                                          int J, long long nvox, float mult) {
+  __shared__ float s_spec[kCoordSpec];
   const int b = blockIdx.y, chunk = blockIdx.x;
   const long long base = (long long)chunk * kSamChunk;
-  const float* cb = coord + (size_t)b * nvox * 3;
+  stage_spec(cs, b, s_spec);
   float cx[kSamEpt], cy[kSamEpt], cz[kSamEpt];
-#pragma unroll
-  for (int i = 0; i < kSamEpt / 4; ++i) {
-    const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
-    if (VEC && v0 < nvox) {
-      const float4* p = reinterpret_cast<const float4*>(cb + v0 * 3);
-      float4 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
-      cx[i * 4 + 0] = a.x;  cy[i * 4 + 0] = a.y;  cz[i * 4 + 0] = a.z;
-      cx[i * 4 + 1] = a.w;  cy[i * 4 + 1] = bb.x; cz[i * 4 + 1] = bb.y;
-      cx[i * 4 + 2] = bb.z; cy[i * 4 + 2] = bb.w; cz[i * 4 + 2] = c.x;
-      cx[i * 4 + 3] = c.y;  cy[i * 4 + 3] = c.z;  cz[i * 4 + 3] = c.w;
-    } else {
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const long long v = v0 + e;
-        const bool in = v < nvox;
-        cx[i * 4 + e] = in ? __ldg(cb + v * 3) : 0.f;
-        cy[i * 4 + e] = in ? __ldg(cb + v * 3 + 1) : 0.f;
-        cz[i * 4 + e] = in ? __ldg(cb + v * 3 + 2) : 0.f;
-      }
-    }
-  }
+  load_xyz16<VEC>(cs, s_spec, b, base, nvox, cx, cy, cz);
   // rows (saved probabilities and, when present, the dense upstream gradient) are double-buffered in registers:
   // the loads of joint j+1 are in flight while joint j is computed and stored
   auto load_rows = [&](int j, float (&p)[kSamEpt], float (&gp)[kSamEpt]) {
@@ -382,16 +400,19 @@ size_t softargmax_ws_bytes(int B, int J, long long nvox) {
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,
-                                      int J, long long nvox, int softmax, float mult, cudaStream_t st) {
+                                      int J, long long nvox, int softmax, float mult, cudaStream_t st,
+                                      const CoordSpecArg* spec) {
+  const CoordSrc cs{coord, spec ? spec->spec : nullptr, spec ? spec->N1 : 1, spec ? spec->N2 : 1,
+                    spec ? spec->transfer : 0};
   if (B * J == 0) return cudaSuccess;
   if (nvox == 0) {  // empty volume: identity tuples
     return launch_softargmax_merge(nullptr, stats, 0, B * J, softmax, st);
   }
   const int nchunk = sam_chunks(nvox);
-  const bool vec = (nvox % 4) == 0 && al16(vol) && al16(coord);
+  const bool vec = (nvox % 4) == 0 && al16(vol) && (cs.spec != nullptr || al16(coord));
   dim3 grid(nchunk, B);
   float* w = static_cast<float*>(ws);
-#define LT_GO(V_, S_) k_sam_stats<V_, S_><<<grid, kSamThreads, 0, st>>>(vol, coord, w, J, nvox, mult)
+#define LT_GO(V_, S_) k_sam_stats<V_, S_><<<grid, kSamThreads, 0, st>>>(vol, cs, w, J, nvox, mult)
   if (vec) { if (softmax) LT_GO(true, true); else LT_GO(true, false); }
   else     { if (softmax) LT_GO(false, true); else LT_GO(false, false); }
 #undef LT_GO
@@ -446,13 +467,16 @@ cudaError_t launch_softargmax_bwd_dot(const float* prob, const float* grad_prob,
 cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const float* coords,
                                   const float* grad_coords, const float* grad_prob, const float* dots,
                                   float* grad_vol, int B, int J, long long nvox, int softmax, float mult,
-                                  cudaStream_t st) {
+                                  cudaStream_t st, const CoordSpecArg* spec) {
   if (B * J == 0 || nvox == 0) return cudaSuccess;
+  const CoordSrc cs{coord, spec ? spec->spec : nullptr, spec ? spec->N1 : 1, spec ? spec->N2 : 1,
+                    spec ? spec->transfer : 0};
   dim3 grid(sam_chunks(nvox), B);
   const bool gp = grad_prob != nullptr;
-  const bool vec = (nvox % 4) == 0 && al16(prob) && al16(coord) && al16(grad_vol) && (!gp || al16(grad_prob));
+  const bool vec = (nvox % 4) == 0 && al16(prob) && (cs.spec != nullptr || al16(coord)) && al16(grad_vol) &&
+                   (!gp || al16(grad_prob));
 #define LT_GO(V_, S_, G_) \
-  k_sam_bwd<V_, S_, G_><<<grid, kSamThreads, 0, st>>>(prob, coord, coords, grad_coords, grad_prob, dots, grad_vol, J, nvox, mult)
+  k_sam_bwd<V_, S_, G_><<<grid, kSamThreads, 0, st>>>(prob, cs, coords, grad_coords, grad_prob, dots, grad_vol, J, nvox, mult)
   if (vec) {
     if (softmax) { if (gp) LT_GO(true, true, true); else LT_GO(true, true, false); }
     else         { if (gp) LT_GO(true, false, true); else LT_GO(true, false, false); }

@@ -16,6 +16,7 @@
 //     lanes through a per-warp shared-memory descriptor table (offset + 4 tap weights).
 #pragma once
 #include "common.cuh"
+#include "coordspec.cuh"
 #include "kernels.h"
 
 namespace lt {
@@ -53,7 +54,27 @@ struct UnprojArgs {
   int nt0, nt1, nt2, ncb;  // tile grid and channel blocks
   int align_corners;
   long long nvox;
+  const float* spec;   // (B,18) per-item coordinate spec (coordspec.cuh): voxel centres are computed, `coord` is not read
+  int transfer;        // spec mode: CMU -> Human3.6M axis swap
 };
+
+// voxel centre (vi0, vi1, vz) of item b: read from the coordinate volume, or evaluated from the item's spec staged in
+// shared memory (bit-identical to K6's tensor)
+__device__ __forceinline__ void voxel_xyz(const UnprojArgs& a, const float* coord_b, const float* s_spec, int vi0, int vi1,
+                                          int vz, float& x, float& y, float& z) {
+  if (a.spec != nullptr) {
+    float o[3];
+    coord_of_voxel(s_spec, a.transfer, a.N1, vi0, vi1, vz, o);
+    x = o[0]; y = o[1]; z = o[2];
+  } else {
+    const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
+    x = __ldg(cp); y = __ldg(cp + 1); z = __ldg(cp + 2);
+  }
+}
+// the item's spec -> shared memory; call before the CTA-wide barrier that publishes s_proj
+__device__ __forceinline__ void stage_unproj_spec(const UnprojArgs& a, int b, float* s_spec) {
+  if (a.spec != nullptr && threadIdx.x < kCoordSpec) s_spec[threadIdx.x] = __ldg(a.spec + (size_t)b * kCoordSpec + threadIdx.x);
+}
 
 // One (voxel, view) tap set. Mirrors, in order:
 //   multiview.py:96   [x y z 1] @ P.t()   (k-sequential fp32 accumulation like an sgemm inner loop)
@@ -140,7 +161,7 @@ template <int LPV>
 __device__ __forceinline__ void build_descs(const UnprojArgs& a, int b, int i0_warp, int i1_warp, int z0, int r,
                                             const float4* s_proj, float4 (*s_w)[TileGeom<LPV>::kSlots],
                                             int (*s_off)[TileGeom<LPV>::kSlots], int v0, int nv, int zsel, int lane,
-                                            float invH, float invW) {
+                                            float invH, float invW, const float* s_spec) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   const float* coord_b = a.coord + (size_t)b * a.nvox * 3;
@@ -150,10 +171,7 @@ __device__ __forceinline__ void build_descs(const UnprojArgs& a, int b, int i0_w
     const int vi0 = i0_warp + TG::run0(r, gg), vi1 = i1_warp + TG::run1(r, gg), vz = z0 + j;
     const bool ok = (vi0 < a.N0) && (vi1 < a.N1) && (vz < a.N2);
     float x = 0.f, y = 0.f, z = 0.f;
-    if (ok) {
-      const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
-      x = __ldg(cp); y = __ldg(cp + 1); z = __ldg(cp + 2);
-    }
+    if (ok) voxel_xyz(a, coord_b, s_spec, vi0, vi1, vz, x, y, z);
     for (int vv = 0; vv < nv; ++vv) {
       int off = -1;
       float4 w = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -58,8 +58,9 @@ struct BwdCtx {
 };
 
 template <int LPV>
-__device__ __forceinline__ BwdCtx bwd_prologue(const UnprojArgs& a, const TileId& T, float4* s_proj) {
+__device__ __forceinline__ BwdCtx bwd_prologue(const UnprojArgs& a, const TileId& T, float4* s_proj, float* s_spec) {
   BwdCtx c;
+  stage_unproj_spec(a, T.b, s_spec);
   c.warp = threadIdx.x >> 5; c.lane = threadIdx.x & 31;
   c.g = c.lane / LPV; c.q = c.lane % LPV;
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
@@ -118,7 +119,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const Un
   auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
   const TileId T = decode_tile(a);
-  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj);
+  __shared__ float s_spec[kCoordSpec];
+  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj, s_spec);
   const int warp = c.warp, lane = c.lane, g = c.g;
 
 #pragma unroll 1
@@ -132,7 +134,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const Un
       const int nv = min(kViewChunk, a.V - v0);
       __syncwarp();
       build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane,
-                       c.invH, c.invW);
+                       c.invH, c.invW, s_spec);
       __syncwarp();
 
       float cw[kViewChunk][kCPL];   // conf of this chunk            (conf only)
@@ -267,7 +269,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
   auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
   const TileId T = decode_tile(a);
-  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj);
+  __shared__ float s_spec[kCoordSpec];
+  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj, s_spec);
   const int warp = c.warp, lane = c.lane, g = c.g;
 
 #pragma unroll 1
@@ -288,7 +291,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
         const int nv = min(kViewChunk, a.V - v0);
         __syncwarp();
         build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
-                         c.invH, c.invW);
+                         c.invH, c.invW, s_spec);
         __syncwarp();
         for (int vv = 0; vv < nv; ++vv) {
           float s[kCPL];
@@ -321,7 +324,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
         const int nv = min(kViewChunk, a.V - v0);
         __syncwarp();
         build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
-                         c.invH, c.invW);
+                         c.invH, c.invW, s_spec);
         __syncwarp();
         for (int vv = 0; vv < nv; ++vv) {
           const int off = s_off[warp][vv][g];
@@ -403,8 +406,10 @@ size_t unproject_bwd_ws_bytes(int B, int V, int C, int N0, int N1, int N2) {
 
 cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, const float* proj,
                                  const float* coord, const float* conf, float* grad_feat_hwc,
-                                 float* grad_conf, void* conf_ws, const UnprojShape& s, cudaStream_t st) {
+                                 float* grad_conf, void* conf_ws, const UnprojShape& s, cudaStream_t st,
+                                 const CoordSpecArg* spec) {
   UnprojArgs a{};
+  if (spec != nullptr) { a.spec = spec->spec; a.transfer = spec->transfer; }
   a.feat = feat_hwc; a.proj = proj; a.coord = coord; a.conf = conf;
   a.gout = grad_out; a.gfeat = grad_feat_hwc;
   a.B = s.B; a.V = s.V; a.C = s.C; a.Cp = padded_channels(s.C); a.H = s.H; a.W = s.W;

@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
   int4* s_box = reinterpret_cast<int4*>(smem + CF::oBox);
   int* s_n = reinterpret_cast<int*>(smem + CF::oN);
 
+  __shared__ float s_spec[kCoordSpec];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane / kLPV, q = lane % kLPV;
   int t = blockIdx.x;
   const int t2 = t % a.nt2; t /= a.nt2;
@@ -162,17 +163,19 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
     // ---------------- P0: histograms, projection rows, key bounding boxes ----------------
     for (int i = tid; i < kViewChunk * CF::HS / 4; i += NT) reinterpret_cast<int4*>(s_hist)[i] = make_int4(0, 0, 0, 0);
     if (tid < nv * 3) s_proj[tid] = __ldg(reinterpret_cast<const float4*>(a.proj) + ((size_t)b * a.V + v0) * 3 + tid);
+    stage_unproj_spec(a, b, s_spec);
     __syncthreads();
     if (warp == 0) {
       const int vv = lane >> 3, c = lane & 7;
       const int i0 = min(t0 * CF::T0 + ((c & 1) ? CF::T0 - 1 : 0), a.N0 - 1);
       const int i1 = min(t1 * CF::T1 + ((c & 2) ? CF::T1 - 1 : 0), a.N1 - 1);
       const int iz = min(z0 + ((c & 4) ? RUN - 1 : 0), a.N2 - 1);
-      const float* cp = coord_b + (((long long)i0 * a.N1 + i1) * a.N2 + iz) * 3;
+      float cx, cy, cz;
+      voxel_xyz(a, coord_b, s_spec, i0, i1, iz, cx, cy, cz);
       float ix = 0.f, iy = 0.f;
       bool ok = false;
-      if (vv < nv) ok = approx_ixy(__ldg(cp), __ldg(cp + 1), __ldg(cp + 2), s_proj[vv * 3], s_proj[vv * 3 + 1],
-                                   s_proj[vv * 3 + 2], a.H, a.W, a.align_corners, ix, iy);
+      if (vv < nv) ok = approx_ixy(cx, cy, cz, s_proj[vv * 3], s_proj[vv * 3 + 1], s_proj[vv * 3 + 2], a.H, a.W,
+                                   a.align_corners, ix, iy);
       float xmin = ix, xmax = ix, ymin = iy;
       int all_ok = ok ? 1 : 0;
 #pragma unroll
@@ -204,8 +207,8 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
       int off = -1, kr = 0;
       float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
       if (vi0 < a.N0 && vi1 < a.N1 && vz < a.N2) {
-        const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
-        const float x = __ldg(cp), y = __ldg(cp + 1), z = __ldg(cp + 2);
+        float x, y, z;
+        voxel_xyz(a, coord_b, s_spec, vi0, vi1, vz, x, y, z);
         int x0, y0;
         if (make_taps(x, y, z, s_proj[vv * 3], s_proj[vv * 3 + 1], s_proj[vv * 3 + 2], a.H, a.W, invH, invW,
                       a.align_corners, x0, y0, w)) {

@@ -59,6 +59,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
   const int g = lane / LPV, q = lane % LPV;
   const TileId T = decode_tile(a);
 
+  __shared__ float s_spec[kCoordSpec];
+  stage_unproj_spec(a, T.b, s_spec);
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
     s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
   __syncthreads();
@@ -81,7 +83,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
     for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
       const int nv = min(kViewChunk, a.V - v0);
       __syncwarp();
-      build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane, invH, invW);
+      build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane, invH, invW, s_spec);
       __syncwarp();
 
       float cw[kViewChunk][kCPL];
@@ -190,6 +192,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane / LPV, q = lane % LPV;
   const TileId T = decode_tile(a);
+  __shared__ float s_spec[kCoordSpec];
+  stage_unproj_spec(a, T.b, s_spec);
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
     s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
   __syncthreads();
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
       for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
         const int nv = min(kViewChunk, a.V - v0);
         __syncwarp();
-        build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane, invH, invW);
+        build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane, invH, invW, s_spec);
         __syncwarp();
         for (int vv = 0; vv < nv; ++vv) {
           float s[kCPL];
@@ -300,8 +304,10 @@ void fill_unproj_tiling(UnprojArgs& a, int lpv) {
 int unproj_lpv(int Cp) { return Cp >= kMaxLanesPerVoxel * kCPL ? kMaxLanesPerVoxel : Cp / kCPL; }
 
 cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const float* coord,
-                                 const float* conf, float* out, const UnprojShape& s, cudaStream_t st) {
+                                 const float* conf, float* out, const UnprojShape& s, cudaStream_t st,
+                                 const CoordSpecArg* spec) {
   UnprojArgs a{};
+  if (spec != nullptr) { a.spec = spec->spec; a.transfer = spec->transfer; }
   a.feat = feat_hwc; a.proj = proj; a.coord = coord; a.conf = conf; a.out = out;
   a.B = s.B; a.V = s.V; a.C = s.C; a.Cp = padded_channels(s.C); a.H = s.H; a.W = s.W;
   a.N0 = s.N0; a.N1 = s.N1; a.N2 = s.N2; a.align_corners = s.align_corners;

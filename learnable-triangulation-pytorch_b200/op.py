@@ -14,6 +14,7 @@ Everything runs in hand-written sm_100a kernels behind the C ABI of ``include/lt
 import torch
 
 from . import _lib
+from .coordspec import CoordSpec
 
 _AGG = {"sum": 0, "max": 2, "softmax": 3}  # 'conf*' -> 1, see _agg_code
 
@@ -100,9 +101,11 @@ class _Unproject(torch.autograd.Function):
         L = _lib.lib()
         B, V, C, H, W = heatmaps.shape
         N0, N1, N2 = coord.shape[1:4]
+        spec = coord if isinstance(coord, CoordSpec) else None   # coordinates computed in the kernels (coordspec.py)
         with torch.cuda.device(heatmaps.device):
             st = _stream()
-            proj_c, coord_c = _f32c(proj), _f32c(coord)
+            proj_c = _f32c(proj)
+            coord_c = spec.specs if spec is not None else _f32c(coord)
             conf_c = _f32c(conf) if conf is not None else None
             feat = _hwcp_base(heatmaps, 'feat')  # written in the gather layout by K7 (process_features): no K0
             from_hwcp = feat is not None
@@ -112,13 +115,19 @@ class _Unproject(torch.autograd.Function):
                 feat = torch.empty((L.lt_feat_layout_elems(B * V, C, H, W),), device=hm.device, dtype=torch.float32)
                 _lib.check(L.lt_feat_to_hwc(_lib.ptr(hm), _lib.ptr(feat), B * V, C, H, W, st))
             out = torch.empty((B, C, N0, N1, N2), device=feat.device, dtype=torch.float32)
-            _lib.check(L.lt_unproject_fwd(_lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c), _lib.ptr(conf_c),
-                                          _lib.ptr(out), B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
+            if spec is not None:
+                _lib.check(L.lt_unproject_fwd_spec(_lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c),
+                                                   1 if spec.transfer else 0, _lib.ptr(conf_c), _lib.ptr(out), B, V, C,
+                                                   H, W, N0, N1, N2, agg, align_corners, st))
+            else:
+                _lib.check(L.lt_unproject_fwd(_lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c), _lib.ptr(conf_c),
+                                              _lib.ptr(out), B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
         # with features that already are the gather layout `feat` aliases the caller's tensor: save that tensor as well so
         # that autograd's version check catches an in-place edit between forward and backward, as it would in the reference
         ctx.save_for_backward(feat, proj_c, coord_c, conf_c, heatmaps if from_hwcp else None)
         ctx.meta = (B, V, C, H, W, N0, N1, N2, agg, align_corners, heatmaps.dtype,
-                    conf.dtype if conf is not None else None, from_hwcp)
+                    conf.dtype if conf is not None else None, from_hwcp,
+                    None if spec is None else (1 if spec.transfer else 0))
         return out
 
     @staticmethod
@@ -126,7 +135,7 @@ class _Unproject(torch.autograd.Function):
     def backward(ctx, grad_out):
         L = _lib.lib()
         feat, proj_c, coord_c, conf_c, _ = ctx.saved_tensors
-        B, V, C, H, W, N0, N1, N2, agg, align_corners, hm_dtype, conf_dtype, from_hwcp = ctx.meta
+        B, V, C, H, W, N0, N1, N2, agg, align_corners, hm_dtype, conf_dtype, from_hwcp, spec_transfer = ctx.meta
         need_hm, need_conf = ctx.needs_input_grad[0], ctx.needs_input_grad[3] and conf_c is not None
         g_hm = g_conf = None
         if not (need_hm or need_conf):
@@ -140,9 +149,14 @@ class _Unproject(torch.autograd.Function):
                 gconf = torch.empty((B, V, C), device=feat.device, dtype=torch.float32)
                 nbytes = L.lt_unproject_bwd_ws_bytes(B, V, C, N0, N1, N2)
                 ws = torch.empty((max(nbytes, 4) // 4,), device=feat.device, dtype=torch.float32)
-            _lib.check(L.lt_unproject_bwd(_lib.ptr(go), _lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c),
-                                          _lib.ptr(conf_c), _lib.ptr(gfeat), _lib.ptr(gconf), _lib.ptr(ws),
-                                          B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
+            if spec_transfer is not None:
+                _lib.check(L.lt_unproject_bwd_spec(_lib.ptr(go), _lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c),
+                                                   spec_transfer, _lib.ptr(conf_c), _lib.ptr(gfeat), _lib.ptr(gconf),
+                                                   _lib.ptr(ws), B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
+            else:
+                _lib.check(L.lt_unproject_bwd(_lib.ptr(go), _lib.ptr(feat), _lib.ptr(proj_c), _lib.ptr(coord_c),
+                                              _lib.ptr(conf_c), _lib.ptr(gfeat), _lib.ptr(gconf), _lib.ptr(ws),
+                                              B, V, C, H, W, N0, N1, N2, agg, align_corners, st))
             if need_hm and from_hwcp:
                 # the producer (K7's backward) reads the gradient map in place: hand its interior back as a view
                 _hwcp_register(gfeat, 'grad')
@@ -164,6 +178,8 @@ def unproject_heatmaps(heatmaps, proj_matricies, coord_volumes, volume_aggregati
     Returns (B,C,N0,N1,N2) float32, always (the reference allocates its output with the default dtype, op.py:104).
     ``align_corners`` (keyword only): None/False = what ``F.grid_sample`` does by default on torch >= 1.3, i.e. what
     the reference computes today; True = the behaviour under its pinned torch 1.0.1.
+    ``coord_volumes`` may also be a ``lt_b200.CoordSpec`` (18 floats per item): the voxel centres are then computed
+    inside the kernels, bit-identical to passing ``spec.materialize()``, and the tensor never exists.
     Differentiable w.r.t. heatmaps and vol_confidences.
     """
     agg = _agg_code(volume_aggregation_method)
@@ -172,7 +188,8 @@ def unproject_heatmaps(heatmaps, proj_matricies, coord_volumes, volume_aggregati
         raise TypeError("'NoneType' object is not subscriptable")
     _require_cuda("heatmaps", heatmaps)
     _require_cuda("proj_matricies", proj_matricies)
-    _require_cuda("coord_volumes", coord_volumes)
+    if not isinstance(coord_volumes, CoordSpec):
+        _require_cuda("coord_volumes", coord_volumes)
     if heatmaps.dim() != 5:
         raise RuntimeError("heatmaps must be (B,V,C,H,W), got {}".format(tuple(heatmaps.shape)))
     B, V = heatmaps.shape[:2]
@@ -197,21 +214,29 @@ class _SoftArgmax(torch.autograd.Function):
     def forward(ctx, volumes, coord, softmax, multiplier):
         L = _lib.lib()
         B, J = volumes.shape[:2]
-        nvox = int(volumes.shape[2]) * int(volumes.shape[3]) * int(volumes.shape[4])
+        N0, N1, N2 = (int(v) for v in volumes.shape[2:])
+        nvox = N0 * N1 * N2
+        spec = coord if isinstance(coord, CoordSpec) else None   # coordinates computed in the kernels (coordspec.py)
         with torch.cuda.device(volumes.device):
             st = _stream()
             vol = _f32c(volumes)
-            coord_c = _f32c(coord)
+            coord_c = spec.specs if spec is not None else _f32c(coord)
             coords = torch.zeros((B, J, 3), device=vol.device, dtype=torch.float32)
             prob = torch.empty(vol.shape, device=vol.device, dtype=torch.float32)
             stats = torch.empty((B, J, 5), device=vol.device, dtype=torch.float32)
             if nvox > 0:
                 nbytes = L.lt_softargmax_ws_bytes(B, J, nvox)
                 ws = torch.empty((max(nbytes, 4) // 4,), device=vol.device, dtype=torch.float32)
-                _lib.check(L.lt_softargmax_fwd(_lib.ptr(vol), _lib.ptr(coord_c), _lib.ptr(coords), _lib.ptr(prob),
-                                               _lib.ptr(stats), _lib.ptr(ws), B, J, nvox, softmax, multiplier, st))
+                if spec is not None:
+                    _lib.check(L.lt_softargmax_fwd_spec(_lib.ptr(vol), _lib.ptr(coord_c), 1 if spec.transfer else 0,
+                                                        _lib.ptr(coords), _lib.ptr(prob), _lib.ptr(stats), _lib.ptr(ws),
+                                                        B, J, N0, N1, N2, softmax, multiplier, st))
+                else:
+                    _lib.check(L.lt_softargmax_fwd(_lib.ptr(vol), _lib.ptr(coord_c), _lib.ptr(coords), _lib.ptr(prob),
+                                                   _lib.ptr(stats), _lib.ptr(ws), B, J, nvox, softmax, multiplier, st))
         ctx.save_for_backward(prob, coord_c, coords)
-        ctx.meta = (B, J, nvox, softmax, multiplier, volumes.dtype)
+        ctx.meta = (B, J, nvox, softmax, multiplier, volumes.dtype,
+                    None if spec is None else (1 if spec.transfer else 0, N0, N1, N2))
         ctx.set_materialize_grads(False)
         return coords.to(volumes.dtype), prob.to(volumes.dtype)
 
@@ -220,7 +245,7 @@ class _SoftArgmax(torch.autograd.Function):
     def backward(ctx, g_coords, g_prob):
         L = _lib.lib()
         prob, coord_c, coords = ctx.saved_tensors
-        B, J, nvox, softmax, multiplier, dtype = ctx.meta
+        B, J, nvox, softmax, multiplier, dtype, spec_meta = ctx.meta
         if not ctx.needs_input_grad[0]:
             return None, None, None, None
         with torch.cuda.device(prob.device):
@@ -238,9 +263,14 @@ class _SoftArgmax(torch.autograd.Function):
                 ws = torch.empty((max(nbytes, 4) // 4,), device=prob.device, dtype=torch.float32)
                 _lib.check(L.lt_softargmax_bwd_dot(_lib.ptr(prob), _lib.ptr(gp), _lib.ptr(dots), _lib.ptr(ws),
                                                    B, J, nvox, st))
-            _lib.check(L.lt_softargmax_bwd(_lib.ptr(prob), _lib.ptr(coord_c), _lib.ptr(coords), _lib.ptr(gc),
-                                           _lib.ptr(gp), _lib.ptr(dots), _lib.ptr(gvol), B, J, nvox, softmax,
-                                           multiplier, st))
+            if spec_meta is not None:
+                _lib.check(L.lt_softargmax_bwd_spec(_lib.ptr(prob), _lib.ptr(coord_c), spec_meta[0], _lib.ptr(coords),
+                                                    _lib.ptr(gc), _lib.ptr(gp), _lib.ptr(dots), _lib.ptr(gvol), B, J,
+                                                    spec_meta[1], spec_meta[2], spec_meta[3], softmax, multiplier, st))
+            else:
+                _lib.check(L.lt_softargmax_bwd(_lib.ptr(prob), _lib.ptr(coord_c), _lib.ptr(coords), _lib.ptr(gc),
+                                               _lib.ptr(gp), _lib.ptr(dots), _lib.ptr(gvol), B, J, nvox, softmax,
+                                               multiplier, st))
         return gvol.to(dtype), None, None, None
 
 
@@ -253,7 +283,8 @@ def integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True, *
     that the caller does before the call (triangulation.py:353). Gradient flows from both outputs into ``volumes``.
     """
     _require_cuda("volumes", volumes)
-    _require_cuda("coord_volumes", coord_volumes)
+    if not isinstance(coord_volumes, CoordSpec):   # a CoordSpec: the centres are computed inside the kernels
+        _require_cuda("coord_volumes", coord_volumes)
     if volumes.dim() != 5:
         raise RuntimeError("volumes must be (B,J,N0,N1,N2), got {}".format(tuple(volumes.shape)))
     B = volumes.shape[0]

@@ -12,7 +12,7 @@ import torch
 from . import _lib
 from .op import _stream
 
-COORD_SPEC = 18
+from .coordspec import COORD_SPEC, CoordSpec  # noqa: F401
 
 
 def rotation_matrix(axis, theta):

@@ -38,7 +38,7 @@ def test_python_binding_covers_header():
 
 def test_host_side_entry_points_without_gpu():
     L = _lib.lib()
-    assert L.lt_abi_version() == 1
+    assert L.lt_abi_version() == 2
     assert L.lt_padded_channels(32) == 32 and L.lt_padded_channels(17) == 32
     assert L.lt_padded_channels(33) == 64 and L.lt_padded_channels(256) == 256 and L.lt_padded_channels(300) == 384
     assert L.lt_softargmax_ws_bytes(16, 17, 64 ** 3) == 16 * 17 * 128 * 8 * 5 * 4   # 2048-voxel chunks, 8 warps, 5 floats
