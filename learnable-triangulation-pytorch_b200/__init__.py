@@ -15,7 +15,7 @@ the repository root registers it under that name).
     lt_b200.slab.integrate_tensor_3d_with_coordinates_sharded   (z-slab multi-GPU variant, one small exchange)
     lt_b200.patch_reference()                          monkey-patches the names above into ``mvn``
 """
-from . import _lib, coordspec, loss, multiview, op, slab, synthetic, triangulation, volumetric  # noqa: F401
+from . import _lib, coordspec, loss, multiview, op, slab, synthetic, torch_ops, triangulation, volumetric  # noqa: F401
 from .coordspec import CoordSpec  # noqa: F401
 from .volumetric import build_coord_volumes  # noqa: F401
 from .loss import VolumetricCELoss, integrate_tensor_3d_with_coordinates_and_ce, volumetric_ce_loss  # noqa: F401

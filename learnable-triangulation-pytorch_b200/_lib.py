@@ -87,7 +87,8 @@ def lib():
             raise RuntimeError(
                 "lt_b200: CUDA library %s is missing and there is no CPU fallback. Build it with "
                 "`make -C %s` (needs nvcc, sm_100a)." % (LIB_PATH, CSRC_DIR))
-        handle = ctypes.CDLL(LIB_PATH)
+        # RTLD_GLOBAL: the torch extension (torch_ops.py) resolves its lt_* symbols against this library at load time
+        handle = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)  # AttributeError here = header/library mismatch
             fn.restype = res

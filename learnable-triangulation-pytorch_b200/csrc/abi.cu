@@ -130,11 +130,17 @@ LT_API int lt_softargmax_finalize(const float* vol, const float* stats, float* c
 
 LT_API int lt_softargmax_fwd(const float* vol, const float* coord, float* coords, float* prob, float* stats, void* ws,
                       int B, int J, long long nvox, int softmax, float multiplier, void* stream) {
-  // (Running partial+finalize per L2-sized group of batch items, so that the second read of the volumes hits L2, was
-  //  measured on B200 and is slower at every group size: the per-group launches no longer fill 148 SMs.)
-  int rc = lt_softargmax_partial(vol, coord, stats, ws, B, J, nvox, softmax, multiplier, stream);
-  if (rc) return rc;
-  return lt_softargmax_finalize(vol, stats, coords, prob, B, J, nvox, softmax, multiplier, stream);
+  // One persistent launch (softargmax.cu, k_sam_fwd_fused): the statistics of item b+1 run between the two passes of
+  // item b, so the second read of the volumes is an L2 hit. (Running partial+finalize per L2-sized group of batch
+  // items as separate launches was measured slower at every group size: the launches no longer fill 148 SMs.)
+  LT_REQUIRE(B >= 0 && J >= 0 && nvox >= 0, "negative extent");
+  LT_REQUIRE(B <= 65535 && (long long)B * J <= 65535, "B*J > 65535");
+  LT_REQUIRE(multiplier > 0.f, "multiplier must be > 0 (scale on the caller side otherwise)");
+  if (B * J == 0) return 0;
+  LT_REQUIRE(stats && (nvox == 0 || (vol && coord && ws)), "null pointer");
+  LT_REQUIRE(((uintptr_t)ws & 15) == 0, "ws must be 16-byte aligned");
+  return finish(__func__, lt::launch_softargmax_fwd(vol, coord, coords, nvox == 0 ? nullptr : prob, stats, ws, B, J, nvox,
+                                                    softmax ? 1 : 0, multiplier, as_stream(stream)));
 }
 
 LT_API int lt_softargmax_merge(const float* parts, float* merged, int R, int BJ, int softmax, void* stream) {
@@ -253,9 +259,17 @@ LT_API int lt_softargmax_partial_spec(const float* vol, const float* coord_spec,
 LT_API int lt_softargmax_fwd_spec(const float* vol, const float* coord_spec, int transfer, float* coords, float* prob,
                            float* stats, void* ws, int B, int J, int N0, int N1, int N2, int softmax,
                            float multiplier, void* stream) {
-  int rc = lt_softargmax_partial_spec(vol, coord_spec, transfer, stats, ws, B, J, N0, N1, N2, softmax, multiplier, stream);
-  if (rc) return rc;
-  return lt_softargmax_finalize(vol, stats, coords, prob, B, J, (long long)N0 * N1 * N2, softmax, multiplier, stream);
+  LT_REQUIRE(B >= 0 && J >= 0, "negative extent");
+  LT_REQUIRE(!bad_spec_volume(N0, N1, N2, transfer), "more than 2^31 voxels per item, or transfer with N1 != N2");
+  LT_REQUIRE(B <= 65535 && (long long)B * J <= 65535, "B*J > 65535");
+  LT_REQUIRE(multiplier > 0.f, "multiplier must be > 0 (scale on the caller side otherwise)");
+  if (B * J == 0) return 0;
+  const long long nvox = (long long)N0 * N1 * N2;
+  LT_REQUIRE(stats && (nvox == 0 || (vol && coord_spec && ws)), "null pointer");
+  LT_REQUIRE(((uintptr_t)ws & 15) == 0, "ws must be 16-byte aligned");
+  const lt::CoordSpecArg cs{coord_spec, N1, N2, transfer ? 1 : 0};
+  return finish(__func__, lt::launch_softargmax_fwd(vol, nullptr, coords, nvox == 0 ? nullptr : prob, stats, ws, B, J,
+                                                    nvox, softmax ? 1 : 0, multiplier, as_stream(stream), &cs));
 }
 
 LT_API int lt_softargmax_bwd_spec(const float* prob, const float* coord_spec, int transfer, const float* coords,

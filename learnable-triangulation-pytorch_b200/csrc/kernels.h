@@ -8,6 +8,7 @@ namespace lt {
 constexpr int kAggSum = 0, kAggConf = 1, kAggMax = 2, kAggSoftmax = 3;  // == enum lt_agg
 
 int padded_channels(int C);
+int sm_count();  // SMs of the current device (148 on B200), queried once per device
 size_t feat_layout_elems(int BV, int C, int H, int W);
 cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwcp,
                                cudaStream_t st);
@@ -44,6 +45,9 @@ cudaError_t launch_softargmax_partial(const float* vol, const float* coord, floa
 cudaError_t launch_softargmax_finalize(const float* vol, const float* stats, float* coords, float* prob,
                                        int B, int J, long long nvox, int softmax, float mult,
                                        cudaStream_t st);
+cudaError_t launch_softargmax_fwd(const float* vol, const float* coord, float* coords, float* prob, float* stats,
+                                  void* ws, int B, int J, long long nvox, int softmax, float mult, cudaStream_t st,
+                                  const CoordSpecArg* spec = nullptr);
 cudaError_t launch_softargmax_merge(const float* parts, float* merged, int R, int BJ, int softmax,
                                     cudaStream_t st);
 cudaError_t launch_softargmax_bwd_dot(const float* prob, const float* grad_prob, float* dots, void* ws,

@@ -109,6 +109,18 @@ cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int 
   return cudaGetLastError();
 }
 
+// SM count of the current device, queried once per device (148 on B200): persistent kernels size their grids with it
+int sm_count() {
+  static int cached[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    cached[dev] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
+  }
+  return cached[dev];
+}
+
 // ---- one-time opt-in for more than 48 KB of dynamic shared memory (see common.cuh) ----
 cudaError_t smem_opt_in(const void* func, size_t bytes) {
   struct Entry { const void* func; int dev; size_t bytes; };

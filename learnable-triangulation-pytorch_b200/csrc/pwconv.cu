@@ -1044,18 +1044,6 @@ inline bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 constexpr int kFwdSmem = kStages * (kKc * kPx + kKc * kCo) * 4;      // 73,728 B -> 3 CTAs per SM
 constexpr int kBwdDataSmem = (kCo * kPx + kCo * kKn) * 4;            // 65,536 B -> 3 CTAs per SM
 constexpr int kBwdWeightSmem = kWgStages * kWgStageFloats * 4;       // 90,112 B -> 2 CTAs per SM
-// SM count of the current device, queried once per device (148 on B200): the persistent kernels launch one CTA per SM
-int sm_count() {
-  static int cached[64] = {};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-  if (cached[dev] == 0) {
-    int n = 0;
-    cached[dev] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
-  }
-  return cached[dev];
-}
-
 // developer knob for A/B measurements (tools/bench_process_features.py): LT_B200_PWCONV=ffma keeps the forward on the
 // FMA pipe. Read once; both paths compute the same fp32 result to 1e-6.
 bool force_ffma() {

@@ -13,6 +13,8 @@
 //   k_sam_final   : prob = e^(x-m)/S, streaming; coords = (Sx,Sy,Sz)/S.
 // exp is evaluated as ex2(fma(x, mult*log2e, -m*log2e)): one FFMA + one MUFU per element; the shift is
 // common to numerator and denominator so only the rounding of log2e (3e-8 * |x-m|) enters the result.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "coordspec.cuh"
 #include "kernels.h"
@@ -35,10 +37,10 @@ static inline int sam_chunks(long long nvox) { return (int)((nvox + kSamChunk - 
 
 // xyz of this thread's 16 voxels: group i covers voxels base + (i*256 + tid)*4 .. +3. Either read from the coordinate
 // volume (128-bit loads when VEC) or evaluated from the item's 18-float spec (coordspec.cuh): same values bit for bit.
-template <bool VEC>
+template <bool VEC, bool SPEC>
 __device__ __forceinline__ void load_xyz16(const CoordSrc& cs, const float* s_spec, int b, long long base, long long nvox,
                                            float (&cx)[kSamEpt], float (&cy)[kSamEpt], float (&cz)[kSamEpt]) {
-  if (cs.spec != nullptr) {
+  if (SPEC) {
 #pragma unroll
     for (int i = 0; i < kSamEpt / 4; ++i) {
       const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
@@ -80,8 +82,9 @@ __device__ __forceinline__ void load_xyz16(const CoordSrc& cs, const float* s_sp
   }
 }
 // the item's spec -> shared memory (no-op in tensor mode); every thread of the CTA must call it
+template <bool SPEC>
 __device__ __forceinline__ void stage_spec(const CoordSrc& cs, int b, float* s_spec) {
-  if (cs.spec != nullptr) {
+  if (SPEC) {
     if (threadIdx.x < kCoordSpec) s_spec[threadIdx.x] = __ldg(cs.spec + (size_t)b * kCoordSpec + threadIdx.x);
     __syncthreads();
   }
@@ -91,22 +94,20 @@ __device__ __forceinline__ void stage_spec(const CoordSrc& cs, int b, float* s_s
 // ---------------------------------------------------------------------------------------------------
 // pass 1: partial tuples. ws layout: [(b*J + j)][chunk*kSamWarps + warp][5]
 // VEC: nvox % 4 == 0 (rows 16-byte aligned) -> 128-bit loads.
-template <bool VEC, bool SOFTMAX>
-__global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __restrict__ vol, const CoordSrc cs,
-                                                           float* __restrict__ ws, int J, long long nvox,
-                                                           float mult) {
-  __shared__ float s_spec[kCoordSpec];
-  const int b = blockIdx.y, chunk = blockIdx.x, nchunk = gridDim.x;
+template <bool VEC, bool SOFTMAX, bool SPEC>
+__device__ __forceinline__ void sam_stats_body(const float* __restrict__ vol, const CoordSrc& cs, float* s_spec,
+                                               float* __restrict__ ws, int J, long long nvox, float mult, int b,
+                                               int chunk, int nchunk) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long base = (long long)chunk * kSamChunk;
-  stage_spec(cs, b, s_spec);
+  stage_spec<SPEC>(cs, b, s_spec);
 
   float cx[kSamEpt], cy[kSamEpt], cz[kSamEpt];
   bool ok[kSamEpt / 4];
 #pragma unroll
   for (int i = 0; i < kSamEpt / 4; ++i)
     ok[i] = VEC && (base + ((long long)i * kSamThreads + threadIdx.x) * 4 < nvox);
-  load_xyz16<VEC>(cs, s_spec, b, base, nvox, cx, cy, cz);
+  load_xyz16<VEC, SPEC>(cs, s_spec, b, base, nvox, cx, cy, cz);
 
   const float L = mult * kLog2e;
   // rows are double-buffered in registers: the loads of joint j+1 are in flight while joint j is reduced
@@ -175,6 +176,14 @@ __global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __res
   }
 }
 
+template <bool VEC, bool SOFTMAX, bool SPEC>
+__global__ void __launch_bounds__(kSamThreads, 4) k_sam_stats(const float* __restrict__ vol, const CoordSrc cs,
+                                                           float* __restrict__ ws, int J, long long nvox,
+                                                           float mult) {
+  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
+  sam_stats_body<VEC, SOFTMAX, SPEC>(vol, cs, s_spec, ws, J, nvox, mult, blockIdx.y, blockIdx.x, gridDim.x);
+}
+
 // merge P tuples per (b,j): one CTA each (a 256^3 volume has 65536 partial tuples per joint), threads stride over the
 // tuples, then a fixed warp butterfly and a fixed-order merge of the warp results: deterministic.
 constexpr int kCombThreads = 256;
@@ -220,18 +229,17 @@ __global__ void __launch_bounds__(kCombThreads) k_sam_combine(const float* __res
 }
 
 // pass 2: prob = e^(mult*x - m)/S (softmax) or relu(mult*x); coords = (Sx,Sy,Sz)/S.
-template <bool VEC, bool SOFTMAX>
-__global__ void __launch_bounds__(kSamThreads) k_sam_final(const float* __restrict__ vol,
-                                                           const float* __restrict__ stats,
-                                                           float* __restrict__ coords, float* __restrict__ prob,
-                                                           long long nvox, float mult) {
-  // reverse traversal: the rows the statistics pass read LAST are the ones still in L2, so they are re-read FIRST
-  const int bj = gridDim.y - 1 - blockIdx.y, chunk = gridDim.x - 1 - blockIdx.x;
+// (stats are read with ld.global.cg: in the fused kernel below they were written by another CTA of the same launch)
+template <bool VEC, bool SOFTMAX, bool COHERENT>
+__device__ __forceinline__ void sam_final_body(const float* __restrict__ vol, const float* stats,
+                                               float* __restrict__ coords, float* __restrict__ prob, long long nvox,
+                                               float mult, int bj, int chunk) {
   const float* st = stats + (size_t)bj * 5;
-  const float m = __ldg(st), S = __ldg(st + 1);
+  auto ld = [](const float* p) { return COHERENT ? __ldcg(p) : __ldg(p); };  // __ldg: L1-resident broadcast
+  const float m = ld(st), S = ld(st + 1);
   const float invS = SOFTMAX ? __fdiv_rn(1.f, S) : 1.f;
   if (chunk == 0 && threadIdx.x < 3 && coords != nullptr)
-    coords[(size_t)bj * 3 + threadIdx.x] = SOFTMAX ? __fdiv_rn(__ldg(st + 2 + threadIdx.x), S) : __ldg(st + 2 + threadIdx.x);
+    coords[(size_t)bj * 3 + threadIdx.x] = SOFTMAX ? __fdiv_rn(ld(st + 2 + threadIdx.x), S) : ld(st + 2 + threadIdx.x);
   if (prob == nullptr) return;
   const float L = mult * kLog2e, shift = -m * kLog2e;
   const float* row = vol + (size_t)bj * nvox;
@@ -263,12 +271,148 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_final(const float* __restri
   }
 }
 
+template <bool VEC, bool SOFTMAX>
+__global__ void __launch_bounds__(kSamThreads) k_sam_final(const float* __restrict__ vol,
+                                                           const float* __restrict__ stats,
+                                                           float* __restrict__ coords, float* __restrict__ prob,
+                                                           long long nvox, float mult) {
+  // reverse traversal: the rows the statistics pass read LAST are the ones still in L2, so they are re-read FIRST
+  sam_final_body<VEC, SOFTMAX, false>(vol, stats, coords, prob, nvox, mult, gridDim.y - 1 - blockIdx.y,
+                               gridDim.x - 1 - blockIdx.x);
+}
+
+// merge of one item's P tuples per joint by ONE CTA: warp <-> joint, lanes stride the tuples, fixed butterfly.
+// Kept out of line: it runs once per item and must not cost the streaming loops of the fused kernel registers.
+template <bool SOFTMAX>
+__device__ __noinline__ void sam_merge_item(const float* ws, float* stats, int b, int J, int P) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int j = warp; j < J; j += kSamWarps) {   // warp <-> joint; lanes stride the tuples; fixed butterfly
+    const float* p = ws + ((size_t)b * J + j) * P * 5;
+    Lse5 acc = SOFTMAX ? lse_identity() : Lse5{0.f, 1.f, 0.f, 0.f, 0.f};
+    for (int i = lane; i < P; i += 32) {
+      const float* t = p + (size_t)i * 5;
+      const Lse5 o = {__ldcg(t), __ldcg(t + 1), __ldcg(t + 2), __ldcg(t + 3), __ldcg(t + 4)};
+      if (SOFTMAX) acc = lse_merge(acc, o);
+      else { acc.x += o.x; acc.y += o.y; acc.z += o.z; }
+    }
+    if (SOFTMAX) acc = lse_warp_reduce(acc);
+    else acc = {0.f, 1.f, warp_sum(acc.x), warp_sum(acc.y), warp_sum(acc.z)};
+    if (lane == 0) {
+      float* o = stats + ((size_t)b * J + j) * 5;
+      o[0] = acc.m; o[1] = acc.s; o[2] = acc.x; o[3] = acc.y; o[4] = acc.z;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// forward on one device as ONE persistent launch: the statistics of item b+1 run between the statistics and the
+// normalisation pass of item b, so the second read of an item's volumes (J*nvox*4 bytes, 17.8 MB at 64^3) is served by
+// L2 instead of HBM (the three-launch version re-reads 285 MB at cfg3: 1.39x the algorithmic bytes).
+// Work units of 2048 voxels x all joints are handed out IN ORDER by a ticket counter:
+//   S(0), S(1), F(0), S(2), F(1), ..., S(B-1), F(B-2), F(B-1)
+// S = statistics (k_sam_stats' body); the CTA that finishes an item's last S unit merges the item's tuples in a fixed
+// order (deterministic, same tree for every run) and raises the item's flag; F = normalisation (k_sam_final's body for
+// every joint of the chunk) after the flag is up. A unit only ever waits for units with smaller tickets, which running
+// CTAs already hold: no deadlock however few CTAs are resident.
+// ctrl: [0] ticket, [1, 1+B) finished S units per item, [1+B, 1+2B) flags; zeroed by the launcher.
+template <bool VEC, bool SOFTMAX, bool SPEC>
+__global__ void __launch_bounds__(kSamThreads, 4) k_sam_fwd_fused(const float* __restrict__ vol, const CoordSrc cs,
+                                                                  float* ws, float* stats, float* __restrict__ coords,
+                                                                  float* __restrict__ prob, int* ctrl, int B, int J,
+                                                                  long long nvox, float mult, int nchunk) {
+  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
+  __shared__ int s_unit, s_last;
+  const int total = 2 * B * nchunk, P = nchunk * kSamWarps;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (;;) {
+    __syncthreads();  // s_unit / s_spec of the previous unit are dead
+    if (threadIdx.x == 0) s_unit = atomicAdd(&ctrl[0], 1);
+    __syncthreads();
+    const int unit = s_unit;
+    if (unit >= total) return;
+    const int g = unit / nchunk, chunk = unit % nchunk;
+    const bool is_stats = (g == 0) || (g != 2 * B - 1 && (g & 1));
+    const int b = (g == 0) ? 0 : (g == 2 * B - 1 ? B - 1 : ((g & 1) ? (g + 1) / 2 : g / 2 - 1));
+    if (is_stats) {
+      sam_stats_body<VEC, SOFTMAX, SPEC>(vol, cs, s_spec, ws, J, nvox, mult, b, chunk, nchunk);
+      __threadfence();
+      __syncthreads();
+      if (threadIdx.x == 0) s_last = (atomicAdd(&ctrl[1 + b], 1) == nchunk - 1);
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        sam_merge_item<SOFTMAX>(ws, stats, b, J, P);
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) atomicExch(&ctrl[1 + B + b], 1);
+      }
+    } else {
+      if (threadIdx.x == 0) {
+        while (atomicAdd(&ctrl[1 + B + b], 0) == 0) __nanosleep(200);
+        __threadfence();
+      }
+      __syncthreads();
+      if (VEC) {
+        // the chunk's rows of kFuseJ joints at a time: all their loads are in flight before the first exponential
+        // (one joint per round trip left this unit latency-bound: 17 dependent L2 round trips per chunk)
+        constexpr int kFuseJ = 4;
+        const long long base = (long long)chunk * kSamChunk;
+        const float L = mult * kLog2e;
+        for (int j0 = 0; j0 < J; j0 += kFuseJ) {
+          float4 t[kFuseJ][kSamEpt / 4];
+#pragma unroll
+          for (int jj = 0; jj < kFuseJ; ++jj) {
+            const float* row = vol + ((size_t)b * J + min(j0 + jj, J - 1)) * nvox;
+#pragma unroll
+            for (int i = 0; i < kSamEpt / 4; ++i) {
+              const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+              t[jj][i] = v0 < nvox ? ldg128_stream(row + v0) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+          }
+#pragma unroll
+          for (int jj = 0; jj < kFuseJ; ++jj) {
+            if (j0 + jj < J) {
+              const int bj = b * J + j0 + jj;
+              const float* st = stats + (size_t)bj * 5;
+              const float m = __ldcg(st), S = __ldcg(st + 1);
+              const float invS = SOFTMAX ? __fdiv_rn(1.f, S) : 1.f, shift = -m * kLog2e;
+              if (chunk == 0 && threadIdx.x < 3)
+                coords[(size_t)bj * 3 + threadIdx.x] =
+                    SOFTMAX ? __fdiv_rn(__ldcg(st + 2 + threadIdx.x), S) : __ldcg(st + 2 + threadIdx.x);
+              float* orow = prob + (size_t)bj * nvox;
+#pragma unroll
+              for (int i = 0; i < kSamEpt / 4; ++i) {
+                const long long v0 = base + ((long long)i * kSamThreads + threadIdx.x) * 4;
+                if (v0 < nvox) {
+                  const float4 x = t[jj][i];
+                  float4 o;
+                  if (SOFTMAX) {
+                    o.x = ex2_approx(fmaf(x.x, L, shift)) * invS; o.y = ex2_approx(fmaf(x.y, L, shift)) * invS;
+                    o.z = ex2_approx(fmaf(x.z, L, shift)) * invS; o.w = ex2_approx(fmaf(x.w, L, shift)) * invS;
+                  } else {
+                    o.x = fmaxf(x.x * mult, 0.f); o.y = fmaxf(x.y * mult, 0.f);
+                    o.z = fmaxf(x.z * mult, 0.f); o.w = fmaxf(x.w * mult, 0.f);
+                  }
+                  stg128_stream(orow + v0, o);
+                }
+              }
+            }
+          }
+        }
+      } else {
+        for (int j = 0; j < J; ++j)
+          sam_final_body<VEC, SOFTMAX, true>(vol, stats, coords, prob, nvox, mult, b * J + j, chunk);
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------
 // backward
 //   softmax: g_i = mult * p_i * (gp_i + gc.xyz_i - dot),  dot = sum_k p_k gp_k + gc.coords
 //   relu   : g_i = mult * [p_i > 0] * (gp_i + gc.xyz_i)
 // grid (chunk, b): coordinates in registers, loop over joints (same reuse as k_sam_stats).
-template <bool VEC, bool SOFTMAX, bool HAS_GP>
+template <bool VEC, bool SOFTMAX, bool HAS_GP, bool SPEC>
 __global__ void __launch_bounds__(kSamThreads) k_sam_bwd(const float* __restrict__ prob,
                                                          const CoordSrc cs,
                                                          const float* __restrict__ coords_out,
@@ -276,12 +420,12 @@ __global__ void __launch_bounds__(kSamThreads) k_sam_bwd(const float* __restrict
                                                          const float* __restrict__ gprob,
                                                          const float* __restrict__ dots, float* __restrict__ gvol,
                                                          int J, long long nvox, float mult) {
-  __shared__ float s_spec[kCoordSpec];
+  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
   const int b = blockIdx.y, chunk = blockIdx.x;
   const long long base = (long long)chunk * kSamChunk;
-  stage_spec(cs, b, s_spec);
+  stage_spec<SPEC>(cs, b, s_spec);
   float cx[kSamEpt], cy[kSamEpt], cz[kSamEpt];
-  load_xyz16<VEC>(cs, s_spec, b, base, nvox, cx, cy, cz);
+  load_xyz16<VEC, SPEC>(cs, s_spec, b, base, nvox, cx, cy, cz);
   // rows (saved probabilities and, when present, the dense upstream gradient) are double-buffered in registers:
   // the loads of joint j+1 are in flight while joint j is computed and stored
   auto load_rows = [&](int j, float (&p)[kSamEpt], float (&gp)[kSamEpt]) {
@@ -392,8 +536,11 @@ __global__ void k_sam_dot_combine(const float* __restrict__ ws, float* __restric
 }
 
 // ---------------------------------------------------------------------------------------------------
+static inline size_t sam_tuple_bytes(int B, int J, long long nvox) {
+  return (((size_t)B * J * sam_chunks(nvox) * kSamWarps * 5 * sizeof(float)) + 255) / 256 * 256;
+}
 size_t softargmax_ws_bytes(int B, int J, long long nvox) {
-  return (size_t)B * J * sam_chunks(nvox) * kSamWarps * 5 * sizeof(float);
+  return sam_tuple_bytes(B, J, nvox) + (size_t)(1 + 2 * B) * sizeof(int);  // + the fused forward's control words
 }
 
 // the 128-bit paths need 16-byte aligned bases on top of nvox % 4 == 0 (include/lt_b200.h "alignment")
@@ -412,7 +559,11 @@ cudaError_t launch_softargmax_partial(const float* vol, const float* coord, floa
   const bool vec = (nvox % 4) == 0 && al16(vol) && (cs.spec != nullptr || al16(coord));
   dim3 grid(nchunk, B);
   float* w = static_cast<float*>(ws);
-#define LT_GO(V_, S_) k_sam_stats<V_, S_><<<grid, kSamThreads, 0, st>>>(vol, cs, w, J, nvox, mult)
+#define LT_GO(V_, S_)                                                                                         \
+  do {                                                                                                        \
+    if (cs.spec != nullptr) k_sam_stats<V_, S_, true><<<grid, kSamThreads, 0, st>>>(vol, cs, w, J, nvox, mult); \
+    else k_sam_stats<V_, S_, false><<<grid, kSamThreads, 0, st>>>(vol, cs, w, J, nvox, mult);                 \
+  } while (0)
   if (vec) { if (softmax) LT_GO(true, true); else LT_GO(true, false); }
   else     { if (softmax) LT_GO(false, true); else LT_GO(false, false); }
 #undef LT_GO
@@ -421,6 +572,45 @@ cudaError_t launch_softargmax_partial(const float* vol, const float* coord, floa
   const int P = nchunk * kSamWarps, BJ = B * J;
   if (softmax) k_sam_combine<true><<<BJ, kCombThreads, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
   else k_sam_combine<false><<<BJ, kCombThreads, 0, st>>>(w, stats, P, BJ, (size_t)P * 5, 5);
+  return cudaGetLastError();
+}
+
+// forward on one device: three launches, or (LT_B200_K2FWD=fused) the persistent fused kernel above
+cudaError_t launch_softargmax_fwd(const float* vol, const float* coord, float* coords, float* prob, float* stats,
+                                  void* ws, int B, int J, long long nvox, int softmax, float mult, cudaStream_t st,
+                                  const CoordSpecArg* spec) {
+  // MEASURED at cfg3 (gpurun_out r2e): the fused launch runs 0.289 ms against 0.165 ms for the three launches (the merge
+  // of an item's tuples by its last CTA sits on the critical path of a two-item-deep pipeline), so it is opt-in:
+  // LT_B200_K2FWD=fused.
+  static const bool split = [] { const char* e = getenv("LT_B200_K2FWD"); return !(e != nullptr && e[0] == 'f'); }();
+  if (split || B * J == 0 || nvox == 0 || prob == nullptr || coords == nullptr) {
+    cudaError_t e = launch_softargmax_partial(vol, coord, stats, ws, B, J, nvox, softmax, mult, st, spec);
+    if (e != cudaSuccess) return e;
+    return launch_softargmax_finalize(vol, stats, coords, prob, B, J, nvox, softmax, mult, st);
+  }
+  const CoordSrc cs{coord, spec ? spec->spec : nullptr, spec ? spec->N1 : 1, spec ? spec->N2 : 1,
+                    spec ? spec->transfer : 0};
+  const int nchunk = sam_chunks(nvox);
+  int* ctrl = reinterpret_cast<int*>(static_cast<char*>(ws) + sam_tuple_bytes(B, J, nvox));
+  cudaError_t e = cudaMemsetAsync(ctrl, 0, (size_t)(1 + 2 * B) * sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  const bool vec = (nvox % 4) == 0 && al16(vol) && al16(prob) && (cs.spec != nullptr || al16(coord));
+  const long long total = 2LL * B * nchunk;
+  const long long resident = 4LL * sm_count();
+  const int grid = (int)(total < resident ? total : resident);
+  float* w = static_cast<float*>(ws);
+#define LT_GO(V_, S_)                                                                                                \
+  do {                                                                                                               \
+    if (cs.spec != nullptr)                                                                                          \
+      k_sam_fwd_fused<V_, S_, true><<<grid, kSamThreads, 0, st>>>(vol, cs, w, stats, coords, prob, ctrl, B, J, nvox, \
+                                                                  mult, nchunk);                                     \
+    else                                                                                                             \
+      k_sam_fwd_fused<V_, S_, false><<<grid, kSamThreads, 0, st>>>(vol, cs, w, stats, coords, prob, ctrl, B, J, nvox, \
+                                                                   mult, nchunk);                                    \
+  } while (0)
+  if (vec) { if (softmax) LT_GO(true, true); else LT_GO(true, false); }
+  else     { if (softmax) LT_GO(false, true); else LT_GO(false, false); }
+#undef LT_GO
   return cudaGetLastError();
 }
 
@@ -475,8 +665,15 @@ cudaError_t launch_softargmax_bwd(const float* prob, const float* coord, const f
   const bool gp = grad_prob != nullptr;
   const bool vec = (nvox % 4) == 0 && al16(prob) && (cs.spec != nullptr || al16(coord)) && al16(grad_vol) &&
                    (!gp || al16(grad_prob));
-#define LT_GO(V_, S_, G_) \
-  k_sam_bwd<V_, S_, G_><<<grid, kSamThreads, 0, st>>>(prob, cs, coords, grad_coords, grad_prob, dots, grad_vol, J, nvox, mult)
+#define LT_GO(V_, S_, G_)                                                                                             \
+  do {                                                                                                                \
+    if (cs.spec != nullptr)                                                                                           \
+      k_sam_bwd<V_, S_, G_, true><<<grid, kSamThreads, 0, st>>>(prob, cs, coords, grad_coords, grad_prob, dots, grad_vol, \
+                                                                J, nvox, mult);                                       \
+    else                                                                                                              \
+      k_sam_bwd<V_, S_, G_, false><<<grid, kSamThreads, 0, st>>>(prob, cs, coords, grad_coords, grad_prob, dots,      \
+                                                                 grad_vol, J, nvox, mult);                            \
+  } while (0)
   if (vec) {
     if (softmax) { if (gp) LT_GO(true, true, true); else LT_GO(true, true, false); }
     else         { if (gp) LT_GO(true, false, true); else LT_GO(true, false, false); }

@@ -60,9 +60,12 @@ struct UnprojArgs {
 
 // voxel centre (vi0, vi1, vz) of item b: read from the coordinate volume, or evaluated from the item's spec staged in
 // shared memory (bit-identical to K6's tensor)
+// SPEC is a compile-time switch: the tensor path must not carry the spec path's registers (measured: a run-time branch
+// cost the 64-register forward kernel spills and 8 % of its time).
+template <bool SPEC>
 __device__ __forceinline__ void voxel_xyz(const UnprojArgs& a, const float* coord_b, const float* s_spec, int vi0, int vi1,
                                           int vz, float& x, float& y, float& z) {
-  if (a.spec != nullptr) {
+  if (SPEC) {
     float o[3];
     coord_of_voxel(s_spec, a.transfer, a.N1, vi0, vi1, vz, o);
     x = o[0]; y = o[1]; z = o[2];
@@ -157,7 +160,7 @@ __device__ __forceinline__ TileId decode_tile(const UnprojArgs& a) {
 
 // phase A: descriptors of this warp's round-r voxels x nv views -> per-warp smem table.
 // zsel < 0: all 8 z steps, slot = j*G + g (G*8 slots, one per lane for C=32); zsel >= 0: only that z step, slot = g.
-template <int LPV>
+template <int LPV, bool SPEC = false>
 __device__ __forceinline__ void build_descs(const UnprojArgs& a, int b, int i0_warp, int i1_warp, int z0, int r,
                                             const float4* s_proj, float4 (*s_w)[TileGeom<LPV>::kSlots],
                                             int (*s_off)[TileGeom<LPV>::kSlots], int v0, int nv, int zsel, int lane,
@@ -171,7 +174,7 @@ __device__ __forceinline__ void build_descs(const UnprojArgs& a, int b, int i0_w
     const int vi0 = i0_warp + TG::run0(r, gg), vi1 = i1_warp + TG::run1(r, gg), vz = z0 + j;
     const bool ok = (vi0 < a.N0) && (vi1 < a.N1) && (vz < a.N2);
     float x = 0.f, y = 0.f, z = 0.f;
-    if (ok) voxel_xyz(a, coord_b, s_spec, vi0, vi1, vz, x, y, z);
+    if (ok) voxel_xyz<SPEC>(a, coord_b, s_spec, vi0, vi1, vz, x, y, z);
     for (int vv = 0; vv < nv; ++vv) {
       int off = -1;
       float4 w = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -57,10 +57,10 @@ struct BwdCtx {
   float* gb;
 };
 
-template <int LPV>
+template <int LPV, bool SPEC>
 __device__ __forceinline__ BwdCtx bwd_prologue(const UnprojArgs& a, const TileId& T, float4* s_proj, float* s_spec) {
   BwdCtx c;
-  stage_unproj_spec(a, T.b, s_spec);
+  if (SPEC) stage_unproj_spec(a, T.b, s_spec);
   c.warp = threadIdx.x >> 5; c.lane = threadIdx.x & 31;
   c.g = c.lane / LPV; c.q = c.lane % LPV;
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
@@ -107,7 +107,7 @@ __device__ __forceinline__ void stage_grad_out(const UnprojArgs& a, int b, int c
 }
 
 // sum / conf for any V; softmax / max for V <= kViewChunk (all samples of a voxel live in registers).
-template <int LPV, int AGG, bool ALIGNED>
+template <int LPV, int AGG, bool ALIGNED, bool SPEC>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
@@ -119,8 +119,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const Un
   auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
   const TileId T = decode_tile(a);
-  __shared__ float s_spec[kCoordSpec];
-  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj, s_spec);
+  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
+  const BwdCtx c = bwd_prologue<LPV, SPEC>(a, T, s_proj, s_spec);
   const int warp = c.warp, lane = c.lane, g = c.g;
 
 #pragma unroll 1
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const Un
     for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
       const int nv = min(kViewChunk, a.V - v0);
       __syncwarp();
-      build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane,
+      build_descs<LPV, SPEC>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane,
                        c.invH, c.invW, s_spec);
       __syncwarp();
 
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const Un
 
 // softmax / max over MORE than kViewChunk views: per z step, pass 1 = running (max, argmax, sum e, sum e*s)
 // over all views, pass 2 = recompute each view's sample and scatter its share.
-template <int LPV, int AGG, bool ALIGNED>
+template <int LPV, int AGG, bool ALIGNED, bool SPEC>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyviews(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int SLOTS = TG::kSlots;
@@ -269,8 +269,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
   auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
   const TileId T = decode_tile(a);
-  __shared__ float s_spec[kCoordSpec];
-  const BwdCtx c = bwd_prologue<LPV>(a, T, s_proj, s_spec);
+  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
+  const BwdCtx c = bwd_prologue<LPV, SPEC>(a, T, s_proj, s_spec);
   const int warp = c.warp, lane = c.lane, g = c.g;
 
 #pragma unroll 1
@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
       for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
         const int nv = min(kViewChunk, a.V - v0);
         __syncwarp();
-        build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
+        build_descs<LPV, SPEC>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
                          c.invH, c.invW, s_spec);
         __syncwarp();
         for (int vv = 0; vv < nv; ++vv) {
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
       for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
         const int nv = min(kViewChunk, a.V - v0);
         __syncwarp();
-        build_descs<LPV>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
+        build_descs<LPV, SPEC>(a, T.b, c.i0_warp, c.i1_warp, c.z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane,
                          c.invH, c.invW, s_spec);
         __syncwarp();
         for (int vv = 0; vv < nv; ++vv) {
@@ -363,7 +363,7 @@ __global__ void k_conf_reduce(const float* __restrict__ part, float* __restrict_
   gconf[i] = s;
 }
 
-template <int LPV>
+template <int LPV, bool SPEC>
 static cudaError_t launch_bwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
   const bool aligned = (a.N2 % kRun) == 0 && (reinterpret_cast<uintptr_t>(a.gout) & 31u) == 0;
   const dim3 block(kWarpsPerCta * 32);
@@ -373,11 +373,11 @@ static cudaError_t launch_bwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaS
 #define LT_LAUNCH(K, AGG_)                                                                    \
   do {                                                                                        \
     if (aligned) {                                                                            \
-      LT_SMEM_OPT_IN_ONCE((K<LPV, AGG_, true>), smem);                                        \
-      K<LPV, AGG_, true><<<grid, block, smem, st>>>(a);                                       \
+      LT_SMEM_OPT_IN_ONCE((K<LPV, AGG_, true, SPEC>), smem);                                  \
+      K<LPV, AGG_, true, SPEC><<<grid, block, smem, st>>>(a);                                 \
     } else {                                                                                  \
-      LT_SMEM_OPT_IN_ONCE((K<LPV, AGG_, false>), smem);                                       \
-      K<LPV, AGG_, false><<<grid, block, smem, st>>>(a);                                      \
+      LT_SMEM_OPT_IN_ONCE((K<LPV, AGG_, false, SPEC>), smem);                                 \
+      K<LPV, AGG_, false, SPEC><<<grid, block, smem, st>>>(a);                                \
     }                                                                                         \
   } while (0)
   switch (agg) {
@@ -439,10 +439,14 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
   dim3 grid((unsigned)nblk);
   cudaError_t e = cudaErrorInvalidValue;
-  switch (lpv) {
-    case 8: e = launch_bwd_lpv<8>(a, s.agg, grid, st); break;
-    case 16: e = launch_bwd_lpv<16>(a, s.agg, grid, st); break;
-    case 32: e = launch_bwd_lpv<32>(a, s.agg, grid, st); break;
+  if (a.spec != nullptr) {
+    e = lpv == 8 ? launch_bwd_lpv<8, true>(a, s.agg, grid, st) : cudaErrorNotSupported;
+  } else {
+    switch (lpv) {
+      case 8: e = launch_bwd_lpv<8, false>(a, s.agg, grid, st); break;
+      case 16: e = launch_bwd_lpv<16, false>(a, s.agg, grid, st); break;
+      case 32: e = launch_bwd_lpv<32, false>(a, s.agg, grid, st); break;
+    }
   }
   if (e != cudaSuccess) return e;
   if (a.gconf_part != nullptr) {

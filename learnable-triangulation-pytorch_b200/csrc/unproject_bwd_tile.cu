@@ -123,7 +123,7 @@ __device__ __forceinline__ void fma4(float4& acc, float w, const float4& d) {
   acc.x = fmaf(w, d.x, acc.x); acc.y = fmaf(w, d.y, acc.y); acc.z = fmaf(w, d.z, acc.z); acc.w = fmaf(w, d.w, acc.w);
 }
 
-template <class CF, int AGG>
+template <class CF, int AGG, bool SPEC>
 __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const UnprojArgs a) {
   constexpr int TV = CF::TV, NB = CF::NB, NT = CF::NT, RUN = CF::RUN, NG = CF::NG;
   extern __shared__ __align__(128) unsigned char smem[];
@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
   int4* s_box = reinterpret_cast<int4*>(smem + CF::oBox);
   int* s_n = reinterpret_cast<int*>(smem + CF::oN);
 
-  __shared__ float s_spec[kCoordSpec];
+  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane / kLPV, q = lane % kLPV;
   int t = blockIdx.x;
   const int t2 = t % a.nt2; t /= a.nt2;
@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
     // ---------------- P0: histograms, projection rows, key bounding boxes ----------------
     for (int i = tid; i < kViewChunk * CF::HS / 4; i += NT) reinterpret_cast<int4*>(s_hist)[i] = make_int4(0, 0, 0, 0);
     if (tid < nv * 3) s_proj[tid] = __ldg(reinterpret_cast<const float4*>(a.proj) + ((size_t)b * a.V + v0) * 3 + tid);
-    stage_unproj_spec(a, b, s_spec);
+    if (SPEC) stage_unproj_spec(a, b, s_spec);
     __syncthreads();
     if (warp == 0) {
       const int vv = lane >> 3, c = lane & 7;
@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
       const int i1 = min(t1 * CF::T1 + ((c & 2) ? CF::T1 - 1 : 0), a.N1 - 1);
       const int iz = min(z0 + ((c & 4) ? RUN - 1 : 0), a.N2 - 1);
       float cx, cy, cz;
-      voxel_xyz(a, coord_b, s_spec, i0, i1, iz, cx, cy, cz);
+      voxel_xyz<SPEC>(a, coord_b, s_spec, i0, i1, iz, cx, cy, cz);
       float ix = 0.f, iy = 0.f;
       bool ok = false;
       if (vv < nv) ok = approx_ixy(cx, cy, cz, s_proj[vv * 3], s_proj[vv * 3 + 1], s_proj[vv * 3 + 2], a.H, a.W,
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
       float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
       if (vi0 < a.N0 && vi1 < a.N1 && vz < a.N2) {
         float x, y, z;
-        voxel_xyz(a, coord_b, s_spec, vi0, vi1, vz, x, y, z);
+        voxel_xyz<SPEC>(a, coord_b, s_spec, vi0, vi1, vz, x, y, z);
         int x0, y0;
         if (make_taps(x, y, z, s_proj[vv * 3], s_proj[vv * 3 + 1], s_proj[vv * 3 + 2], a.H, a.W, invH, invW,
                       a.align_corners, x0, y0, w)) {
@@ -505,8 +505,13 @@ cudaError_t launch_one(UnprojArgs& a, const UnprojShape& s, cudaStream_t st) {
   a.ncb = 1;
   const long long nblk = (long long)a.B * a.nt0 * a.nt1 * a.nt2;
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
-  LT_SMEM_OPT_IN_ONCE((k_unproject_bwd_tile<CF, AGG>), CF::kBytes);
-  k_unproject_bwd_tile<CF, AGG><<<(unsigned)nblk, CF::NT, CF::kBytes, st>>>(a);
+  if (a.spec != nullptr) {
+    LT_SMEM_OPT_IN_ONCE((k_unproject_bwd_tile<CF, AGG, true>), CF::kBytes);
+    k_unproject_bwd_tile<CF, AGG, true><<<(unsigned)nblk, CF::NT, CF::kBytes, st>>>(a);
+  } else {
+    LT_SMEM_OPT_IN_ONCE((k_unproject_bwd_tile<CF, AGG, false>), CF::kBytes);
+    k_unproject_bwd_tile<CF, AGG, false><<<(unsigned)nblk, CF::NT, CF::kBytes, st>>>(a);
+  }
   return cudaGetLastError();
 }
 

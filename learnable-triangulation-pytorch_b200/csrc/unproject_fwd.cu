@@ -42,7 +42,7 @@ __device__ __forceinline__ void softmax_mix4_x2(const float (&a)[4], const float
 #ifndef LT_K1F_CTAS
 #define LT_K1F_CTAS 4
 #endif
-template <int LPV, int AGG, bool ALIGNED>
+template <int LPV, int AGG, bool ALIGNED, bool SPEC>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fwd(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
@@ -59,8 +59,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
   const int g = lane / LPV, q = lane % LPV;
   const TileId T = decode_tile(a);
 
-  __shared__ float s_spec[kCoordSpec];
-  stage_unproj_spec(a, T.b, s_spec);
+  __shared__ float s_spec_mem[SPEC ? kCoordSpec : 1];
+  const float* s_spec = SPEC ? s_spec_mem : nullptr;
+  if (SPEC) stage_unproj_spec(a, T.b, s_spec_mem);
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
     s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
   __syncthreads();
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
     for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
       const int nv = min(kViewChunk, a.V - v0);
       __syncwarp();
-      build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane, invH, invW, s_spec);
+      build_descs<LPV, SPEC>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, -1, lane, invH, invW, s_spec);
       __syncwarp();
 
       float cw[kViewChunk][kCPL];
@@ -181,7 +182,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
 
 // softmax over MORE than kViewChunk views: running (m, sum e, sum e*s) per channel; z step outermost so the state
 // stays at 3 x 4 registers and phase A covers G voxels x nv views per round. Same tiling, same descriptors.
-template <int LPV, bool ALIGNED>
+template <int LPV, bool ALIGNED, bool SPEC>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_manyviews(const UnprojArgs a) {
   using TG = TileGeom<LPV>;
   constexpr int SLOTS = TG::kSlots;
@@ -192,8 +193,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane / LPV, q = lane % LPV;
   const TileId T = decode_tile(a);
-  __shared__ float s_spec[kCoordSpec];
-  stage_unproj_spec(a, T.b, s_spec);
+  __shared__ float s_spec_mem[SPEC ? kCoordSpec : 1];
+  const float* s_spec = SPEC ? s_spec_mem : nullptr;
+  if (SPEC) stage_unproj_spec(a, T.b, s_spec_mem);
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
     s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
   __syncthreads();
@@ -221,7 +223,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
       for (int v0 = 0; v0 < a.V; v0 += kViewChunk) {
         const int nv = min(kViewChunk, a.V - v0);
         __syncwarp();
-        build_descs<LPV>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane, invH, invW, s_spec);
+        build_descs<LPV, SPEC>(a, T.b, i0_warp, i1_warp, z0, r, s_proj, s_w[warp], s_off[warp], v0, nv, j, lane, invH, invW, s_spec);
         __syncwarp();
         for (int vv = 0; vv < nv; ++vv) {
           float s[kCPL];
@@ -262,7 +264,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
   }
 }
 
-template <int LPV>
+template <int LPV, bool SPEC>
 static cudaError_t launch_fwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
   const bool aligned = (a.N2 % kRun) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 31u) == 0;
   const dim3 block(kWarpsPerCta * 32);
@@ -272,11 +274,11 @@ static cudaError_t launch_fwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaS
 #define LT_LAUNCH(AGG_)                                                           \
   do {                                                                            \
     if (aligned) {                                                                \
-      LT_SMEM_OPT_IN_ONCE((k_unproject_fwd<LPV, AGG_, true>), smem);              \
-      k_unproject_fwd<LPV, AGG_, true><<<grid, block, smem, st>>>(a);             \
+      LT_SMEM_OPT_IN_ONCE((k_unproject_fwd<LPV, AGG_, true, SPEC>), smem);        \
+      k_unproject_fwd<LPV, AGG_, true, SPEC><<<grid, block, smem, st>>>(a);       \
     } else {                                                                      \
-      LT_SMEM_OPT_IN_ONCE((k_unproject_fwd<LPV, AGG_, false>), smem);             \
-      k_unproject_fwd<LPV, AGG_, false><<<grid, block, smem, st>>>(a);            \
+      LT_SMEM_OPT_IN_ONCE((k_unproject_fwd<LPV, AGG_, false, SPEC>), smem);       \
+      k_unproject_fwd<LPV, AGG_, false, SPEC><<<grid, block, smem, st>>>(a);      \
     }                                                                             \
   } while (0)
   switch (agg) {
@@ -285,8 +287,8 @@ static cudaError_t launch_fwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaS
     case kAggMax: LT_LAUNCH(kAggMax); break;
     case kAggSoftmax:
       if (a.V <= kViewChunk) LT_LAUNCH(kAggSoftmax);
-      else if (aligned) k_unproject_fwd_softmax_manyviews<LPV, true><<<grid, block, 0, st>>>(a);
-      else k_unproject_fwd_softmax_manyviews<LPV, false><<<grid, block, 0, st>>>(a);
+      else if (aligned) k_unproject_fwd_softmax_manyviews<LPV, true, SPEC><<<grid, block, 0, st>>>(a);
+      else k_unproject_fwd_softmax_manyviews<LPV, false, SPEC><<<grid, block, 0, st>>>(a);
       break;
     default: return cudaErrorInvalidValue;
   }
@@ -318,10 +320,12 @@ cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const
   const long long nblk = (long long)a.B * a.ncb * a.nt0 * a.nt1 * a.nt2;
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
   dim3 grid((unsigned)nblk);
+  // coordinates from the spec: instantiated for the reference's 32 channels; wider maps take the tensor (K6) instead
+  if (a.spec != nullptr) return lpv == 8 ? launch_fwd_lpv<8, true>(a, s.agg, grid, st) : cudaErrorNotSupported;
   switch (lpv) {
-    case 8: return launch_fwd_lpv<8>(a, s.agg, grid, st);
-    case 16: return launch_fwd_lpv<16>(a, s.agg, grid, st);
-    case 32: return launch_fwd_lpv<32>(a, s.agg, grid, st);
+    case 8: return launch_fwd_lpv<8, false>(a, s.agg, grid, st);
+    case 16: return launch_fwd_lpv<16, false>(a, s.agg, grid, st);
+    case 32: return launch_fwd_lpv<32, false>(a, s.agg, grid, st);
   }
   return cudaErrorInvalidValue;
 }

@@ -76,6 +76,9 @@ def triangulate_batch_of_points(proj_matricies_batch, points_batch, confidences_
     conf = None
     if confidences_batch is not None:
         conf = confidences_batch[:B].reshape(B, V, J)
+    from . import torch_ops
+    if torch_ops.available():
+        return torch.ops.lt_b200.triangulate_batch_of_points(proj_matricies_batch[:B], points_batch, conf)
     return _DLT.apply(proj_matricies_batch[:B], points_batch, conf)
 
 

@@ -206,6 +206,15 @@ def unproject_heatmaps(heatmaps, proj_matricies, coord_volumes, volume_aggregati
     # the reference only ever indexes [batch_i, view_i] of these (op.py:108,118)
     proj = proj_matricies[:B, :V]
     coord = coord_volumes[:B]
+    from . import torch_ops
+    if torch_ops.available() and _hwcp_base(heatmaps, 'feat') is None:
+        # the torch extension: one dispatcher call, C++ autograd node (torch.ops.lt_b200.unproject_heatmaps)
+        if isinstance(coord, CoordSpec):
+            return torch.ops.lt_b200.unproject_heatmaps(heatmaps, proj, coord.specs, agg, conf, bool(align_corners),
+                                                        list(coord.size), coord.transfer)
+        return torch.ops.lt_b200.unproject_heatmaps(heatmaps, proj, coord, agg, conf, bool(align_corners), [], False)
+    # features already in the gather layout (written by K7, triangulation.process_features), or no extension built:
+    # the ctypes binding of the same kernels
     return _Unproject.apply(heatmaps, proj, coord, conf, agg, 1 if align_corners else 0)
 
 
@@ -297,6 +306,13 @@ def integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True, *
     if not multiplier > 0.0:  # the kernels fold a positive scale into the exponent; anything else is pre-scaled
         volumes = volumes * multiplier
         multiplier = 1.0
+    from . import torch_ops
+    if torch_ops.available():
+        if isinstance(coord_volumes, CoordSpec):
+            return torch.ops.lt_b200.integrate_tensor_3d_with_coordinates(volumes, coord_volumes.specs, bool(softmax),
+                                                                          multiplier, True, coord_volumes.transfer)
+        return torch.ops.lt_b200.integrate_tensor_3d_with_coordinates(volumes, coord_volumes, bool(softmax), multiplier,
+                                                                      False, False)
     return _SoftArgmax.apply(volumes, coord_volumes, 1 if softmax else 0, multiplier)
 
 
