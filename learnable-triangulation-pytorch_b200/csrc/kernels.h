@@ -7,18 +7,18 @@ namespace lt {
 
 constexpr int kAggSum = 0, kAggConf = 1, kAggMax = 2, kAggSoftmax = 3;  // == enum lt_agg
 
-int padded_channels(int C);
-int sm_count();  // SMs of the current device (148 on B200), queried once per device
-size_t feat_layout_elems(int BV, int C, int H, int W);
-cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwcp,
-                               cudaStream_t st);
-
 // coordinates computed in the consuming kernel from the per-item 18-float spec of K6 instead of read from the tensor
 // (coordspec.cuh); N1, N2 = the two inner volume extents, transfer = the CMU -> Human3.6M axis swap
 struct CoordSpecArg {
   const float* spec;  // (B, 18) device pointer
   int N1, N2, transfer;
 };
+
+int padded_channels(int C);
+int sm_count();  // SMs of the current device (148 on B200), queried once per device
+size_t feat_layout_elems(int BV, int C, int H, int W);
+cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int H, int W, bool to_hwcp,
+                               cudaStream_t st);
 
 struct UnprojShape {
   int B, V, C, H, W, N0, N1, N2, agg, align_corners;
@@ -36,7 +36,8 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
 struct UnprojArgs;
 bool unproject_bwd_tile_eligible(const UnprojShape& s, const float* grad_out);
 size_t unproject_bwd_tile_ws_bytes(const UnprojShape& s);
-cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float* grad_conf, cudaStream_t st);
+cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float* grad_conf, cudaStream_t st,
+                                      const CoordSpecArg* spec);
 
 size_t softargmax_ws_bytes(int B, int J, long long nvox);
 cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,

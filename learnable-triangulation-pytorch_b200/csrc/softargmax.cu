@@ -309,7 +309,7 @@ __device__ __noinline__ void sam_merge_item(const float* ws, float* stats, int b
 // normalisation pass of item b, so the second read of an item's volumes (J*nvox*4 bytes, 17.8 MB at 64^3) is served by
 // L2 instead of HBM (the three-launch version re-reads 285 MB at cfg3: 1.39x the algorithmic bytes).
 // Work units of 2048 voxels x all joints are handed out IN ORDER by a ticket counter:
-//   S(0), S(1), F(0), S(2), F(1), ..., S(B-1), F(B-2), F(B-1)
+//   S(0), S(1), F(0), S(2), F(1), ..., S(B-1), F(B-2), F(B-1)      (lag 1; LT_B200_K2LAG=n runs n items of S ahead)
 // S = statistics (k_sam_stats' body); the CTA that finishes an item's last S unit merges the item's tuples in a fixed
 // order (deterministic, same tree for every run) and raises the item's flag; F = normalisation (k_sam_final's body for
 // every joint of the chunk) after the flag is up. A unit only ever waits for units with smaller tickets, which running
@@ -319,11 +319,12 @@ template <bool VEC, bool SOFTMAX, bool SPEC>
 __global__ void __launch_bounds__(kSamThreads, 4) k_sam_fwd_fused(const float* __restrict__ vol, const CoordSrc cs,
                                                                   float* ws, float* stats, float* __restrict__ coords,
                                                                   float* __restrict__ prob, int* ctrl, int B, int J,
-                                                                  long long nvox, float mult, int nchunk) {
+                                                                  long long nvox, float mult, int nchunk, int lag) {
   __shared__ float s_spec[SPEC ? kCoordSpec : 1];
   __shared__ int s_unit, s_last;
   const int total = 2 * B * nchunk, P = nchunk * kSamWarps;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* ws2 = ws + (size_t)B * J * P * 5;  // one tuple per (b, joint, chunk)
   for (;;) {
     __syncthreads();  // s_unit / s_spec of the previous unit are dead
     if (threadIdx.x == 0) s_unit = atomicAdd(&ctrl[0], 1);
@@ -331,17 +332,41 @@ __global__ void __launch_bounds__(kSamThreads, 4) k_sam_fwd_fused(const float* _
     const int unit = s_unit;
     if (unit >= total) return;
     const int g = unit / nchunk, chunk = unit % nchunk;
-    const bool is_stats = (g == 0) || (g != 2 * B - 1 && (g & 1));
-    const int b = (g == 0) ? 0 : (g == 2 * B - 1 ? B - 1 : ((g & 1) ? (g + 1) / 2 : g / 2 - 1));
+    // S(0..L), then F(k), S(L+1+k) alternating, then the last L+1 F groups (L = lag, clamped to B-1)
+    bool is_stats;
+    int b;
+    if (g <= lag) { is_stats = true; b = g; }
+    else {
+      const int h = g - (lag + 1), mid = 2 * (B - lag - 1);
+      if (h < mid) { is_stats = (h & 1) != 0; b = is_stats ? lag + 1 + h / 2 : h / 2; }
+      else { is_stats = false; b = (B - lag - 1) + (h - mid); }
+    }
     if (is_stats) {
       sam_stats_body<VEC, SOFTMAX, SPEC>(vol, cs, s_spec, ws, J, nvox, mult, b, chunk, nchunk);
+      __syncthreads();
+      // first level of the merge, by this CTA: its 8 warp tuples per joint -> one tuple per (joint, chunk) in ws2
+      // (fixed butterfly over 8 lanes), so that the item's last CTA only merges nchunk tuples per joint
+      for (int j = warp; j < J; j += kSamWarps) {
+        const float* t = ws + (((size_t)b * J + j) * P + (size_t)chunk * kSamWarps + (lane & 7)) * 5;
+        Lse5 acc = {__ldcg(t), __ldcg(t + 1), __ldcg(t + 2), __ldcg(t + 3), __ldcg(t + 4)};
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {
+          const Lse5 other = lse_shfl_xor(acc, o);
+          if (SOFTMAX) acc = lse_merge(acc, other);
+          else { acc.x += other.x; acc.y += other.y; acc.z += other.z; }
+        }
+        if (lane == 0) {
+          float* o2 = ws2 + (((size_t)b * J + j) * nchunk + chunk) * 5;
+          o2[0] = acc.m; o2[1] = acc.s; o2[2] = acc.x; o2[3] = acc.y; o2[4] = acc.z;
+        }
+      }
       __threadfence();
       __syncthreads();
       if (threadIdx.x == 0) s_last = (atomicAdd(&ctrl[1 + b], 1) == nchunk - 1);
       __syncthreads();
       if (s_last) {
         __threadfence();
-        sam_merge_item<SOFTMAX>(ws, stats, b, J, P);
+        sam_merge_item<SOFTMAX>(ws2, stats, b, J, nchunk);
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) atomicExch(&ctrl[1 + B + b], 1);
@@ -537,7 +562,8 @@ __global__ void k_sam_dot_combine(const float* __restrict__ ws, float* __restric
 
 // ---------------------------------------------------------------------------------------------------
 static inline size_t sam_tuple_bytes(int B, int J, long long nvox) {
-  return (((size_t)B * J * sam_chunks(nvox) * kSamWarps * 5 * sizeof(float)) + 255) / 256 * 256;
+  // per-warp tuples + (fused forward) one pre-merged tuple per chunk
+  return (((size_t)B * J * sam_chunks(nvox) * (kSamWarps + 1) * 5 * sizeof(float)) + 255) / 256 * 256;
 }
 size_t softargmax_ws_bytes(int B, int J, long long nvox) {
   return sam_tuple_bytes(B, J, nvox) + (size_t)(1 + 2 * B) * sizeof(int);  // + the fused forward's control words
@@ -595,6 +621,8 @@ cudaError_t launch_softargmax_fwd(const float* vol, const float* coord, float* c
   cudaError_t e = cudaMemsetAsync(ctrl, 0, (size_t)(1 + 2 * B) * sizeof(int), st);
   if (e != cudaSuccess) return e;
   const bool vec = (nvox % 4) == 0 && al16(vol) && al16(prob) && (cs.spec != nullptr || al16(coord));
+  static const int lag_env = [] { const char* e = getenv("LT_B200_K2LAG"); return e ? atoi(e) : 1; }();
+  const int lag = lag_env < 0 ? 0 : (lag_env > B - 1 ? B - 1 : lag_env);  // items of statistics ahead of the normalisation
   const long long total = 2LL * B * nchunk;
   const long long resident = 4LL * sm_count();
   const int grid = (int)(total < resident ? total : resident);
@@ -603,10 +631,10 @@ cudaError_t launch_softargmax_fwd(const float* vol, const float* coord, float* c
   do {                                                                                                               \
     if (cs.spec != nullptr)                                                                                          \
       k_sam_fwd_fused<V_, S_, true><<<grid, kSamThreads, 0, st>>>(vol, cs, w, stats, coords, prob, ctrl, B, J, nvox, \
-                                                                  mult, nchunk);                                     \
+                                                                  mult, nchunk, lag);                                \
     else                                                                                                             \
       k_sam_fwd_fused<V_, S_, false><<<grid, kSamThreads, 0, st>>>(vol, cs, w, stats, coords, prob, ctrl, B, J, nvox, \
-                                                                   mult, nchunk);                                    \
+                                                                   mult, nchunk, lag);                               \
   } while (0)
   if (vec) { if (softmax) LT_GO(true, true); else LT_GO(true, false); }
   else     { if (softmax) LT_GO(false, true); else LT_GO(false, false); }

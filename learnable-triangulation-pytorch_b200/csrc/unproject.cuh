@@ -54,20 +54,47 @@ struct UnprojArgs {
   int nt0, nt1, nt2, ncb;  // tile grid and channel blocks
   int align_corners;
   long long nvox;
-  const float* spec;   // (B,18) per-item coordinate spec (coordspec.cuh): voxel centres are computed, `coord` is not read
-  int transfer;        // spec mode: CMU -> Human3.6M axis swap
 };
+
+// Kernel argument block. The SPEC instantiations (voxel centres computed from the per-item spec, coordspec.cuh) carry
+// two more fields; the tensor-path kernels keep exactly UnprojArgs (MEASURED: the two extra fields in a shared struct
+// were enough to make ptxas spill in the 64-register forward kernel: 0.497 -> 0.525 ms at cfg3).
+template <bool SPEC>
+struct KArgs : UnprojArgs {};
+template <>
+struct KArgs<true> : UnprojArgs {
+  const float* spec;   // (B,18): `coord` is not read
+  int transfer;        // CMU -> Human3.6M axis swap
+};
+template <bool SPEC>
+inline KArgs<SPEC> make_kargs(const UnprojArgs& a, const CoordSpecArg* spec);
+template <>
+inline KArgs<false> make_kargs<false>(const UnprojArgs& a, const CoordSpecArg*) {
+  KArgs<false> k;
+  static_cast<UnprojArgs&>(k) = a;
+  return k;
+}
+template <>
+inline KArgs<true> make_kargs<true>(const UnprojArgs& a, const CoordSpecArg* spec) {
+  KArgs<true> k;
+  static_cast<UnprojArgs&>(k) = a;
+  k.spec = spec->spec;
+  k.transfer = spec->transfer;
+  return k;
+}
+__device__ __forceinline__ int kargs_transfer(const KArgs<false>&) { return 0; }
+__device__ __forceinline__ int kargs_transfer(const KArgs<true>& a) { return a.transfer; }
 
 // voxel centre (vi0, vi1, vz) of item b: read from the coordinate volume, or evaluated from the item's spec staged in
 // shared memory (bit-identical to K6's tensor)
 // SPEC is a compile-time switch: the tensor path must not carry the spec path's registers (measured: a run-time branch
 // cost the 64-register forward kernel spills and 8 % of its time).
 template <bool SPEC>
-__device__ __forceinline__ void voxel_xyz(const UnprojArgs& a, const float* coord_b, const float* s_spec, int vi0, int vi1,
+__device__ __forceinline__ void voxel_xyz(const KArgs<SPEC>& a, const float* coord_b, const float* s_spec, int vi0, int vi1,
                                           int vz, float& x, float& y, float& z) {
   if (SPEC) {
     float o[3];
-    coord_of_voxel(s_spec, a.transfer, a.N1, vi0, vi1, vz, o);
+    coord_of_voxel(s_spec, kargs_transfer(a), a.N1, vi0, vi1, vz, o);
     x = o[0]; y = o[1]; z = o[2];
   } else {
     const float* cp = coord_b + (((long long)vi0 * a.N1 + vi1) * a.N2 + vz) * 3;
@@ -75,8 +102,8 @@ __device__ __forceinline__ void voxel_xyz(const UnprojArgs& a, const float* coor
   }
 }
 // the item's spec -> shared memory; call before the CTA-wide barrier that publishes s_proj
-__device__ __forceinline__ void stage_unproj_spec(const UnprojArgs& a, int b, float* s_spec) {
-  if (a.spec != nullptr && threadIdx.x < kCoordSpec) s_spec[threadIdx.x] = __ldg(a.spec + (size_t)b * kCoordSpec + threadIdx.x);
+__device__ __forceinline__ void stage_unproj_spec(const KArgs<true>& a, int b, float* s_spec) {
+  if (threadIdx.x < kCoordSpec) s_spec[threadIdx.x] = __ldg(a.spec + (size_t)b * kCoordSpec + threadIdx.x);
 }
 
 // One (voxel, view) tap set. Mirrors, in order:
@@ -161,7 +188,7 @@ __device__ __forceinline__ TileId decode_tile(const UnprojArgs& a) {
 // phase A: descriptors of this warp's round-r voxels x nv views -> per-warp smem table.
 // zsel < 0: all 8 z steps, slot = j*G + g (G*8 slots, one per lane for C=32); zsel >= 0: only that z step, slot = g.
 template <int LPV, bool SPEC = false>
-__device__ __forceinline__ void build_descs(const UnprojArgs& a, int b, int i0_warp, int i1_warp, int z0, int r,
+__device__ __forceinline__ void build_descs(const KArgs<SPEC>& a, int b, int i0_warp, int i1_warp, int z0, int r,
                                             const float4* s_proj, float4 (*s_w)[TileGeom<LPV>::kSlots],
                                             int (*s_off)[TileGeom<LPV>::kSlots], int v0, int nv, int zsel, int lane,
                                             float invH, float invW, const float* s_spec) {
@@ -213,6 +240,21 @@ __device__ __forceinline__ void gather4(const float* __restrict__ fv, int off, c
   unpack2(lo, s[0], s[1]);
   unpack2(hi, s[2], s[3]);
 }
+
+// shared-memory home of the item's spec: exists only in the SPEC instantiations (a dummy array in the tensor-path
+// kernels was enough to tip the 64-register forward kernel into spilling)
+template <bool SPEC>
+struct SpecSmem {
+  __device__ static __forceinline__ const float* stage(const KArgs<false>&, int) { return nullptr; }
+};
+template <>
+struct SpecSmem<true> {
+  __device__ static __forceinline__ const float* stage(const KArgs<true>& a, int b) {
+    __shared__ float s_spec[kCoordSpec];
+    stage_unproj_spec(a, b, s_spec);
+    return s_spec;
+  }
+};
 
 void fill_unproj_tiling(UnprojArgs& a, int lpv);
 int unproj_lpv(int Cp);

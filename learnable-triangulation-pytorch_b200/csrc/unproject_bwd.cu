@@ -58,9 +58,8 @@ struct BwdCtx {
 };
 
 template <int LPV, bool SPEC>
-__device__ __forceinline__ BwdCtx bwd_prologue(const UnprojArgs& a, const TileId& T, float4* s_proj, float* s_spec) {
+__device__ __forceinline__ BwdCtx bwd_prologue(const KArgs<SPEC>& a, const TileId& T, float4* s_proj) {
   BwdCtx c;
-  if (SPEC) stage_unproj_spec(a, T.b, s_spec);
   c.warp = threadIdx.x >> 5; c.lane = threadIdx.x & 31;
   c.g = c.lane / LPV; c.q = c.lane % LPV;
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
@@ -108,7 +107,7 @@ __device__ __forceinline__ void stage_grad_out(const UnprojArgs& a, int b, int c
 
 // sum / conf for any V; softmax / max for V <= kViewChunk (all samples of a voxel live in registers).
 template <int LPV, int AGG, bool ALIGNED, bool SPEC>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KArgs<SPEC> a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
@@ -119,8 +118,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const Un
   auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
   const TileId T = decode_tile(a);
-  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
-  const BwdCtx c = bwd_prologue<LPV, SPEC>(a, T, s_proj, s_spec);
+  const float* s_spec = SpecSmem<SPEC>::stage(a, T.b);  // published by the barrier inside the prologue
+  const BwdCtx c = bwd_prologue<LPV, SPEC>(a, T, s_proj);
   const int warp = c.warp, lane = c.lane, g = c.g;
 
 #pragma unroll 1
@@ -259,7 +258,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const Un
 // softmax / max over MORE than kViewChunk views: per z step, pass 1 = running (max, argmax, sum e, sum e*s)
 // over all views, pass 2 = recompute each view's sample and scatter its share.
 template <int LPV, int AGG, bool ALIGNED, bool SPEC>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyviews(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyviews(const KArgs<SPEC> a) {
   using TG = TileGeom<LPV>;
   constexpr int SLOTS = TG::kSlots;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -269,8 +268,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
   auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
 
   const TileId T = decode_tile(a);
-  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
-  const BwdCtx c = bwd_prologue<LPV, SPEC>(a, T, s_proj, s_spec);
+  const float* s_spec = SpecSmem<SPEC>::stage(a, T.b);  // published by the barrier inside the prologue
+  const BwdCtx c = bwd_prologue<LPV, SPEC>(a, T, s_proj);
   const int warp = c.warp, lane = c.lane, g = c.g;
 
 #pragma unroll 1
@@ -364,7 +363,8 @@ __global__ void k_conf_reduce(const float* __restrict__ part, float* __restrict_
 }
 
 template <int LPV, bool SPEC>
-static cudaError_t launch_bwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
+static cudaError_t launch_bwd_lpv(const UnprojArgs& ua, const CoordSpecArg* spec, int agg, dim3 grid, cudaStream_t st) {
+  const KArgs<SPEC> a = make_kargs<SPEC>(ua, spec);
   const bool aligned = (a.N2 % kRun) == 0 && (reinterpret_cast<uintptr_t>(a.gout) & 31u) == 0;
   const dim3 block(kWarpsPerCta * 32);
   constexpr int SL = TileGeom<LPV>::kSlots;
@@ -409,7 +409,6 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
                                  float* grad_conf, void* conf_ws, const UnprojShape& s, cudaStream_t st,
                                  const CoordSpecArg* spec) {
   UnprojArgs a{};
-  if (spec != nullptr) { a.spec = spec->spec; a.transfer = spec->transfer; }
   a.feat = feat_hwc; a.proj = proj; a.coord = coord; a.conf = conf;
   a.gout = grad_out; a.gfeat = grad_feat_hwc;
   a.B = s.B; a.V = s.V; a.C = s.C; a.Cp = padded_channels(s.C); a.H = s.H; a.W = s.W;
@@ -426,7 +425,7 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
   if (unproject_bwd_tile_eligible(s, grad_out)) {
     // on-chip merged formulation (unproject_bwd_tile.cu); its grad_conf partials need no zero-fill
     if (want_gconf && s.agg == kAggConf) a.gconf_part = static_cast<float*>(conf_ws);
-    return launch_unproject_bwd_tile(a, s, grad_conf, st);
+    return launch_unproject_bwd_tile(a, s, grad_conf, st, spec);
   }
   if (want_gconf && s.agg == kAggConf) {
     a.gconf_part = static_cast<float*>(conf_ws);
@@ -439,13 +438,13 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
   dim3 grid((unsigned)nblk);
   cudaError_t e = cudaErrorInvalidValue;
-  if (a.spec != nullptr) {
-    e = lpv == 8 ? launch_bwd_lpv<8, true>(a, s.agg, grid, st) : cudaErrorNotSupported;
+  if (spec != nullptr) {
+    e = lpv == 8 ? launch_bwd_lpv<8, true>(a, spec, s.agg, grid, st) : cudaErrorNotSupported;
   } else {
     switch (lpv) {
-      case 8: e = launch_bwd_lpv<8, false>(a, s.agg, grid, st); break;
-      case 16: e = launch_bwd_lpv<16, false>(a, s.agg, grid, st); break;
-      case 32: e = launch_bwd_lpv<32, false>(a, s.agg, grid, st); break;
+      case 8: e = launch_bwd_lpv<8, false>(a, nullptr, s.agg, grid, st); break;
+      case 16: e = launch_bwd_lpv<16, false>(a, nullptr, s.agg, grid, st); break;
+      case 32: e = launch_bwd_lpv<32, false>(a, nullptr, s.agg, grid, st); break;
     }
   }
   if (e != cudaSuccess) return e;

@@ -123,8 +123,13 @@ __device__ __forceinline__ void fma4(float4& acc, float w, const float4& d) {
   acc.x = fmaf(w, d.x, acc.x); acc.y = fmaf(w, d.y, acc.y); acc.z = fmaf(w, d.z, acc.z); acc.w = fmaf(w, d.w, acc.w);
 }
 
+template <bool SPEC>
+__device__ __forceinline__ void stage_spec_if(const KArgs<SPEC>&, int, float*) {}
+template <>
+__device__ __forceinline__ void stage_spec_if<true>(const KArgs<true>& a, int b, float* s) { stage_unproj_spec(a, b, s); }
+
 template <class CF, int AGG, bool SPEC>
-__global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const UnprojArgs a) {
+__global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const KArgs<SPEC> a) {
   constexpr int TV = CF::TV, NB = CF::NB, NT = CF::NT, RUN = CF::RUN, NG = CF::NG;
   extern __shared__ __align__(128) unsigned char smem[];
   float4* s_stage = reinterpret_cast<float4*>(smem + CF::oStage);
@@ -138,7 +143,8 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
   int4* s_box = reinterpret_cast<int4*>(smem + CF::oBox);
   int* s_n = reinterpret_cast<int*>(smem + CF::oN);
 
-  __shared__ float s_spec[SPEC ? kCoordSpec : 1];
+  __shared__ float s_spec_mem[SPEC ? kCoordSpec : 1];
+  const float* s_spec = s_spec_mem;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane / kLPV, q = lane % kLPV;
   int t = blockIdx.x;
   const int t2 = t % a.nt2; t /= a.nt2;
@@ -163,7 +169,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const U
     // ---------------- P0: histograms, projection rows, key bounding boxes ----------------
     for (int i = tid; i < kViewChunk * CF::HS / 4; i += NT) reinterpret_cast<int4*>(s_hist)[i] = make_int4(0, 0, 0, 0);
     if (tid < nv * 3) s_proj[tid] = __ldg(reinterpret_cast<const float4*>(a.proj) + ((size_t)b * a.V + v0) * 3 + tid);
-    if (SPEC) stage_unproj_spec(a, b, s_spec);
+    stage_spec_if<SPEC>(a, b, s_spec_mem);
     __syncthreads();
     if (warp == 0) {
       const int vv = lane >> 3, c = lane & 7;
@@ -500,28 +506,28 @@ long long tile_count(const UnprojShape& s) {
 }
 
 template <class CF, int AGG>
-cudaError_t launch_one(UnprojArgs& a, const UnprojShape& s, cudaStream_t st) {
+cudaError_t launch_one(UnprojArgs& a, const UnprojShape& s, cudaStream_t st, const CoordSpecArg* spec) {
   tile_dims<CF>(s, a.nt0, a.nt1, a.nt2);
   a.ncb = 1;
   const long long nblk = (long long)a.B * a.nt0 * a.nt1 * a.nt2;
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
-  if (a.spec != nullptr) {
+  if (spec != nullptr) {
     LT_SMEM_OPT_IN_ONCE((k_unproject_bwd_tile<CF, AGG, true>), CF::kBytes);
-    k_unproject_bwd_tile<CF, AGG, true><<<(unsigned)nblk, CF::NT, CF::kBytes, st>>>(a);
+    k_unproject_bwd_tile<CF, AGG, true><<<(unsigned)nblk, CF::NT, CF::kBytes, st>>>(make_kargs<true>(a, spec));
   } else {
     LT_SMEM_OPT_IN_ONCE((k_unproject_bwd_tile<CF, AGG, false>), CF::kBytes);
-    k_unproject_bwd_tile<CF, AGG, false><<<(unsigned)nblk, CF::NT, CF::kBytes, st>>>(a);
+    k_unproject_bwd_tile<CF, AGG, false><<<(unsigned)nblk, CF::NT, CF::kBytes, st>>>(make_kargs<false>(a, nullptr));
   }
   return cudaGetLastError();
 }
 
 template <class CF>
-cudaError_t launch_agg(UnprojArgs& a, const UnprojShape& s, cudaStream_t st) {
+cudaError_t launch_agg(UnprojArgs& a, const UnprojShape& s, cudaStream_t st, const CoordSpecArg* spec) {
   switch (s.agg) {
-    case kAggSum: return launch_one<CF, kAggSum>(a, s, st);
-    case kAggConf: return launch_one<CF, kAggConf>(a, s, st);
-    case kAggMax: return launch_one<CF, kAggMax>(a, s, st);
-    case kAggSoftmax: return launch_one<CF, kAggSoftmax>(a, s, st);
+    case kAggSum: return launch_one<CF, kAggSum>(a, s, st, spec);
+    case kAggConf: return launch_one<CF, kAggConf>(a, s, st, spec);
+    case kAggMax: return launch_one<CF, kAggMax>(a, s, st, spec);
+    case kAggSoftmax: return launch_one<CF, kAggSoftmax>(a, s, st, spec);
   }
   return cudaErrorInvalidValue;
 }
@@ -545,13 +551,14 @@ size_t unproject_bwd_tile_ws_bytes(const UnprojShape& s) {
   return (size_t)s.B * (size_t)tile_count(s) * s.V * s.C * sizeof(float);
 }
 
-cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float* grad_conf, cudaStream_t st) {
+cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float* grad_conf, cudaStream_t st,
+                                      const CoordSpecArg* spec) {
   cudaError_t e;
   switch (tile_cfg_id()) {
-    case 1: e = launch_agg<CfgB>(a, s, st); break;
-    case 2: e = launch_agg<CfgC>(a, s, st); break;
-    case 3: e = launch_agg<CfgD>(a, s, st); break;
-    default: e = launch_agg<CfgA>(a, s, st); break;
+    case 1: e = launch_agg<CfgB>(a, s, st, spec); break;
+    case 2: e = launch_agg<CfgC>(a, s, st, spec); break;
+    case 3: e = launch_agg<CfgD>(a, s, st, spec); break;
+    default: e = launch_agg<CfgA>(a, s, st, spec); break;
   }
   if (e != cudaSuccess) return e;
   if (a.gconf_part != nullptr) {

@@ -43,7 +43,7 @@ __device__ __forceinline__ void softmax_mix4_x2(const float (&a)[4], const float
 #define LT_K1F_CTAS 4
 #endif
 template <int LPV, int AGG, bool ALIGNED, bool SPEC>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fwd(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fwd(const KArgs<SPEC> a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
@@ -59,9 +59,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
   const int g = lane / LPV, q = lane % LPV;
   const TileId T = decode_tile(a);
 
-  __shared__ float s_spec_mem[SPEC ? kCoordSpec : 1];
-  const float* s_spec = SPEC ? s_spec_mem : nullptr;
-  if (SPEC) stage_unproj_spec(a, T.b, s_spec_mem);
+  const float* s_spec = SpecSmem<SPEC>::stage(a, T.b);
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
     s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
   __syncthreads();
@@ -183,7 +181,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
 // softmax over MORE than kViewChunk views: running (m, sum e, sum e*s) per channel; z step outermost so the state
 // stays at 3 x 4 registers and phase A covers G voxels x nv views per round. Same tiling, same descriptors.
 template <int LPV, bool ALIGNED, bool SPEC>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_manyviews(const UnprojArgs a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_manyviews(const KArgs<SPEC> a) {
   using TG = TileGeom<LPV>;
   constexpr int SLOTS = TG::kSlots;
   __shared__ float4 s_proj[kMaxViewsSmem * 3];
@@ -193,9 +191,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane / LPV, q = lane % LPV;
   const TileId T = decode_tile(a);
-  __shared__ float s_spec_mem[SPEC ? kCoordSpec : 1];
-  const float* s_spec = SPEC ? s_spec_mem : nullptr;
-  if (SPEC) stage_unproj_spec(a, T.b, s_spec_mem);
+  const float* s_spec = SpecSmem<SPEC>::stage(a, T.b);
   for (int i = threadIdx.x; i < a.V * 3 && i < kMaxViewsSmem * 3; i += blockDim.x)
     s_proj[i] = __ldg(reinterpret_cast<const float4*>(a.proj) + (size_t)T.b * a.V * 3 + i);
   __syncthreads();
@@ -265,7 +261,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
 }
 
 template <int LPV, bool SPEC>
-static cudaError_t launch_fwd_lpv(const UnprojArgs& a, int agg, dim3 grid, cudaStream_t st) {
+static cudaError_t launch_fwd_lpv(const UnprojArgs& ua, const CoordSpecArg* spec, int agg, dim3 grid, cudaStream_t st) {
+  const KArgs<SPEC> a = make_kargs<SPEC>(ua, spec);
   const bool aligned = (a.N2 % kRun) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 31u) == 0;
   const dim3 block(kWarpsPerCta * 32);
   constexpr int SL = TileGeom<LPV>::kSlots;
@@ -309,7 +306,6 @@ cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const
                                  const float* conf, float* out, const UnprojShape& s, cudaStream_t st,
                                  const CoordSpecArg* spec) {
   UnprojArgs a{};
-  if (spec != nullptr) { a.spec = spec->spec; a.transfer = spec->transfer; }
   a.feat = feat_hwc; a.proj = proj; a.coord = coord; a.conf = conf; a.out = out;
   a.B = s.B; a.V = s.V; a.C = s.C; a.Cp = padded_channels(s.C); a.H = s.H; a.W = s.W;
   a.N0 = s.N0; a.N1 = s.N1; a.N2 = s.N2; a.align_corners = s.align_corners;
@@ -321,11 +317,11 @@ cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
   dim3 grid((unsigned)nblk);
   // coordinates from the spec: instantiated for the reference's 32 channels; wider maps take the tensor (K6) instead
-  if (a.spec != nullptr) return lpv == 8 ? launch_fwd_lpv<8, true>(a, s.agg, grid, st) : cudaErrorNotSupported;
+  if (spec != nullptr) return lpv == 8 ? launch_fwd_lpv<8, true>(a, spec, s.agg, grid, st) : cudaErrorNotSupported;
   switch (lpv) {
-    case 8: return launch_fwd_lpv<8, false>(a, s.agg, grid, st);
-    case 16: return launch_fwd_lpv<16, false>(a, s.agg, grid, st);
-    case 32: return launch_fwd_lpv<32, false>(a, s.agg, grid, st);
+    case 8: return launch_fwd_lpv<8, false>(a, nullptr, s.agg, grid, st);
+    case 16: return launch_fwd_lpv<16, false>(a, nullptr, s.agg, grid, st);
+    case 32: return launch_fwd_lpv<32, false>(a, nullptr, s.agg, grid, st);
   }
   return cudaErrorInvalidValue;
 }
