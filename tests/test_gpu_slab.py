@@ -62,14 +62,18 @@ def _worker(rank, world, port, N, softmax, with_gp, q):
         dist.destroy_process_group()
 
 
-def _world_sizes():
+def _cases():
+    """(world, softmax, with_gp): the full cross on two ranks; three ranks (unequal slabs) and every GPU of the box with
+    the softmax + dense-gradient case (each case spawns `world` processes: keep the 8-GPU bill small)."""
     n = torch.cuda.device_count() if torch.cuda.is_available() else 0
-    return [w for w in (2, 3, 4, 8) if w <= n] or [2]
+    cases = [(2, sm, gp) for sm in (True, False) for gp in (False, True)]
+    for w in sorted({3, n} - {2}):
+        if 2 < w <= n:
+            cases.append((w, True, True))
+    return cases
 
 
-@pytest.mark.parametrize("world", _world_sizes())
-@pytest.mark.parametrize("softmax", [True, False])
-@pytest.mark.parametrize("with_gp", [False, True])
+@pytest.mark.parametrize("world,softmax,with_gp", _cases())
 def test_sharded_softargmax_on_real_ranks(world, softmax, with_gp):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d CUDA devices" % world)
