@@ -395,6 +395,48 @@ def bench_process_features(step, w, B, peak, iters=20):
     return res
 
 
+def bench_in_kernel_coordinates(step, w, B, peak, iters=30):
+    """SURVEY 8(f) row 1 beside the path: the four kernels of the step with the voxel centres evaluated in-kernel from
+    the 18-float specs (lt_*_spec entry points) instead of read from the (B,N,N,N,3) tensor. Same launches as the device
+    arm otherwise; CUDA events around `iters` launches each. Algorithmic bytes drop by K = nvox*12 per item and kernel."""
+    from lt_b200 import volumetric
+    L, p = step.L, step.lib.ptr
+    h = step.host
+    N0, N1, N2 = step.N
+    spec = volumetric.coord_volume_specs(h["base_points"], 2500.0, step.N, h["thetas"]).to(step.dev)
+    st = torch.cuda.current_stream().cuda_stream
+    V, C, H, W, J = w["V"], w["C"], w["H"], w["W"], w["J"]
+    calls = {
+        "k1_unproject_fwd": lambda: L.lt_unproject_fwd_spec(p(step.feat_hwc), p(step.proj), p(spec), 0, p(step.conf),
+                                                            p(step.vol), B, V, C, H, W, N0, N1, N2, step.agg, 0, st),
+        "k2_softargmax_fwd": lambda: L.lt_softargmax_fwd_spec(p(step.x), p(spec), 0, p(step.coords), p(step.prob),
+                                                              p(step.stats), p(step.ws), B, J, N0, N1, N2, 1, 1.0, st),
+        "k2_softargmax_bwd": lambda: L.lt_softargmax_bwd_spec(p(step.prob), p(spec), 0, p(step.coords), p(step.gcoords),
+                                                              None, None, p(step.gx), B, J, N0, N1, N2, 1, 1.0, st),
+        "k1_unproject_bwd": lambda: L.lt_unproject_bwd_spec(p(step.gvol), p(step.feat_hwc), p(step.proj), p(spec), 0,
+                                                            p(step.conf), p(step.gfeat_hwc), p(step.gconf), p(step.ws),
+                                                            B, V, C, H, W, N0, N1, N2, step.agg, 0, st),
+    }
+    ab = algorithmic_bytes(w, B)
+    K = B * step.nvox * 12
+    res = {"note": "coordinates computed in-kernel (lt_*_spec); algorithmic bytes = the tensor variant's minus K", "kernels": {}}
+    for name, fn in calls.items():
+        for _ in range(3):
+            rc = fn()
+            if rc != 0:
+                raise RuntimeError("%s returned %d" % (name, rc))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); a.record()
+        for _ in range(iters):
+            fn()
+        b.record(); torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / iters
+        nbytes = ab[name] - K
+        res["kernels"][name] = {"ms": round(ms, 4), "algorithmic_bytes": nbytes, "gbs": round(nbytes / ms * 1e-6, 1),
+                                "frac": round(nbytes / ms * 1e-6 / peak, 4)}
+    return res
+
+
 def bench_sharded_softargmax(rank, world, dev, steps=30, N=256, J=17):
     """BASELINE config 5's soft-argmax across the ranks of this launch, the one path of the product with a collective:
     every rank holds a slab of ONE (1, J, N, N, N) volume (split along the first volume axis), computes its (m, S, Sxyz)
@@ -663,6 +705,10 @@ def main():
             roofline["next_rows"] = {"k7_process_features": bench_process_features(step, w, B, peak)}
         except Exception as exc:  # a side measurement must never cost the bench line
             roofline["next_rows"] = {"k7_process_features": {"error": repr(exc)[:200]}}
+        try:
+            roofline["next_rows"]["in_kernel_coordinates"] = bench_in_kernel_coordinates(step, w, B, peak)
+        except Exception as exc:  # noqa: BLE001
+            roofline["next_rows"]["in_kernel_coordinates"] = {"error": repr(exc)[:200]}
 
     # the one collective of the product (cfg5's z-slab soft-argmax), measured on the ranks of THIS launch with a parity
     # number, whatever the workload: the default multi-GPU line (cfg3) has no collective of its own

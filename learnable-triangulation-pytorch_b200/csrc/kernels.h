@@ -36,6 +36,7 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
 struct UnprojArgs;
 bool unproject_bwd_tile_eligible(const UnprojShape& s, const float* grad_out);
 size_t unproject_bwd_tile_ws_bytes(const UnprojShape& s);
+cudaError_t launch_conf_reduce_rows(const float* part, float* grad_conf, int B, int VC, int nrows, cudaStream_t st);
 cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float* grad_conf, cudaStream_t st,
                                       const CoordSpecArg* spec);
 

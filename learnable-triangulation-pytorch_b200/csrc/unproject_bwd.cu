@@ -16,7 +16,6 @@
 
 namespace lt {
 
-constexpr int kConfSlots = 64;  // grad_conf partial-sum slots per batch item
 
 // scatter-add w_tap * d[0..3] into the four taps; taps with zero weight (outside the map) are skipped.
 __device__ __forceinline__ void scatter4(float* __restrict__ gv, int off, const float4& w, int Cp,
@@ -116,11 +115,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
   auto s_w = reinterpret_cast<float4(*)[kViewChunk][SLOTS]>(s_proj + kMaxViewsSmem * 3);
   auto s_go = reinterpret_cast<float4(*)[kRun][32]>(&s_w[kWarpsPerCta][0][0]);
   auto s_off = reinterpret_cast<int(*)[kViewChunk][SLOTS]>(&s_go[kWarpsPerCta][0][0]);
+  float* s_gc = reinterpret_cast<float*>(&s_off[kWarpsPerCta][0][0]);  // conf only: [warp][view][channel of the block]
 
   const TileId T = decode_tile(a);
   const float* s_spec = SpecSmem<SPEC>::stage(a, T.b);  // published by the barrier inside the prologue
   const BwdCtx c = bwd_prologue<LPV, SPEC>(a, T, s_proj);
   const int warp = c.warp, lane = c.lane, g = c.g;
+  const size_t ntile_rows = (size_t)a.nt0 * a.nt1 * a.nt2 * TG::R;
 
 #pragma unroll 1
   for (int r = 0; r < TG::R; ++r) {
@@ -228,8 +229,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
       }
 
       if (AGG == kAggConf && a.gconf_part != nullptr) {
-        // reduce d conf over the G lane groups of the warp, then one reduction per (view, channel) per warp
-        // into one of kConfSlots partial buffers (summed by k_conf_reduce).
+        // d conf of this (round, view chunk): lane groups of a warp by shuffles, the warps of the CTA through shared
+        // memory in warp order, then ONE plain store per (view, channel) into the row of this (tile, round): the rows are
+        // summed in a fixed order by k_conf_reduce_tiles -> grad_conf is deterministic (no atomics anywhere).
 #pragma unroll
         for (int vv = 0; vv < kViewChunk; ++vv)
 #pragma unroll
@@ -237,18 +239,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
             float v = gcw[vv][k];
 #pragma unroll
             for (int o = LPV; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            gcw[vv][k] = v;
+            if (g == 0) s_gc[(warp * kViewChunk + vv) * (LPV * kCPL) + c.q * kCPL + k] = v;
           }
-        if (g == 0) {
-          const int slot = (T.lin * kWarpsPerCta + warp) % kConfSlots;
-          float* dst = a.gconf_part + (((size_t)T.b * kConfSlots + slot) * a.V + v0) * a.C;
+        __syncthreads();
+        for (int i = threadIdx.x; i < nv * LPV * kCPL; i += blockDim.x) {
+          const int vv = i / (LPV * kCPL), cc = i % (LPV * kCPL);
+          float s = 0.f;
 #pragma unroll
-          for (int vv = 0; vv < kViewChunk; ++vv)
-            if (vv < nv)
-#pragma unroll
-              for (int k = 0; k < kCPL; ++k)
-                if (c.c_lane + k < a.C) atomicAdd(dst + (size_t)vv * a.C + c.c_lane + k, gcw[vv][k]);
+          for (int wi = 0; wi < kWarpsPerCta; ++wi) s += s_gc[(wi * kViewChunk + vv) * (LPV * kCPL) + cc];
+          const int ch = T.cb * (LPV * kCPL) + cc;
+          const size_t row = ((size_t)T.b * ntile_rows + (size_t)T.lin * TG::R + r);
+          if (ch < a.C) a.gconf_part[(row * a.V + v0 + vv) * a.C + ch] = s;
         }
+        __syncthreads();
       }
     }
     __syncwarp();  // s_go of this round is dead before the next round overwrites it (lane-private, but keep order)
@@ -352,26 +355,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
   }
 }
 
-// grad_conf[b,v,c] = sum over the kConfSlots partial buffers
-__global__ void k_conf_reduce(const float* __restrict__ part, float* __restrict__ gconf, int VC, int total) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= total) return;
-  const int b = i / VC, r = i % VC;
-  float s = 0.f;
-  for (int k = 0; k < kConfSlots; ++k) s += part[((size_t)b * kConfSlots + k) * VC + r];
-  gconf[i] = s;
-}
-
 template <int LPV, bool SPEC>
 static cudaError_t launch_bwd_lpv(const UnprojArgs& ua, const CoordSpecArg* spec, int agg, dim3 grid, cudaStream_t st) {
   const KArgs<SPEC> a = make_kargs<SPEC>(ua, spec);
   const bool aligned = (a.N2 % kRun) == 0 && (reinterpret_cast<uintptr_t>(a.gout) & 31u) == 0;
   const dim3 block(kWarpsPerCta * 32);
   constexpr int SL = TileGeom<LPV>::kSlots;
-  constexpr size_t smem = sizeof(float4) * kMaxViewsSmem * 3 + kWarpsPerCta * kViewChunk * SL * (sizeof(float4) + sizeof(int)) +
-                          sizeof(float4) * kWarpsPerCta * kRun * 32;
+  constexpr size_t smem_base = sizeof(float4) * kMaxViewsSmem * 3 +
+                               kWarpsPerCta * kViewChunk * SL * (sizeof(float4) + sizeof(int)) +
+                               sizeof(float4) * kWarpsPerCta * kRun * 32;
+  constexpr size_t smem_conf = sizeof(float) * kWarpsPerCta * kViewChunk * LPV * kCPL;  // grad_conf staging (conf only)
 #define LT_LAUNCH(K, AGG_)                                                                    \
   do {                                                                                        \
+    const size_t smem = smem_base + (AGG_ == kAggConf ? smem_conf : 0);                       \
     if (aligned) {                                                                            \
       LT_SMEM_OPT_IN_ONCE((K<LPV, AGG_, true, SPEC>), smem);                                  \
       K<LPV, AGG_, true, SPEC><<<grid, block, smem, st>>>(a);                                 \
@@ -397,8 +393,13 @@ static cudaError_t launch_bwd_lpv(const UnprojArgs& ua, const CoordSpecArg* spec
   return cudaGetLastError();
 }
 
+#define TILE_ROUNDS(lpv) ((kWarpRuns0 * kWarpRuns1) / (32 / (lpv)))
 size_t unproject_bwd_ws_bytes(int B, int V, int C, int N0, int N1, int N2) {
-  const size_t scatter = (size_t)B * kConfSlots * V * C * sizeof(float);
+  // one row of V*C partial sums per (item, 8x8x8 tile, round of the tile's warps): rounds = lanes per voxel / 4
+  const int lpv_ = unproj_lpv(padded_channels(C));
+  const size_t rows = (size_t)((N0 + kTile0 - 1) / kTile0) * ((N1 + kTile1 - 1) / kTile1) * ((N2 + kRun - 1) / kRun) *
+                      TILE_ROUNDS(lpv_);
+  const size_t scatter = (size_t)B * rows * V * C * sizeof(float);
   const UnprojShape s{B, V, C, 0, 0, N0, N1, N2, kAggConf, 0};
   const size_t tile = unproject_bwd_tile_ws_bytes(s);  // whichever kernel the launch picks, the buffer is big enough
   return scatter > tile ? scatter : tile;
@@ -427,11 +428,7 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
     if (want_gconf && s.agg == kAggConf) a.gconf_part = static_cast<float*>(conf_ws);
     return launch_unproject_bwd_tile(a, s, grad_conf, st, spec);
   }
-  if (want_gconf && s.agg == kAggConf) {
-    a.gconf_part = static_cast<float*>(conf_ws);
-    cudaError_t e = cudaMemsetAsync(conf_ws, 0, (size_t)s.B * kConfSlots * s.V * s.C * sizeof(float), st);
-    if (e != cudaSuccess) return e;
-  }
+  if (want_gconf && s.agg == kAggConf) a.gconf_part = static_cast<float*>(conf_ws);  // every row is fully written
   const int lpv = unproj_lpv(a.Cp);
   fill_unproj_tiling(a, lpv);
   const long long nblk = (long long)a.B * a.ncb * a.nt0 * a.nt1 * a.nt2;
@@ -448,11 +445,8 @@ cudaError_t launch_unproject_bwd(const float* grad_out, const float* feat_hwc, c
     }
   }
   if (e != cudaSuccess) return e;
-  if (a.gconf_part != nullptr) {
-    const int total = (int)nconf;
-    k_conf_reduce<<<(total + 255) / 256, 256, 0, st>>>(a.gconf_part, grad_conf, s.V * s.C, total);
-    e = cudaGetLastError();
-  }
+  if (a.gconf_part != nullptr)
+    e = launch_conf_reduce_rows(a.gconf_part, grad_conf, s.B, s.V * s.C, a.nt0 * a.nt1 * a.nt2 * TILE_ROUNDS(lpv), st);
   return e;
 }
 

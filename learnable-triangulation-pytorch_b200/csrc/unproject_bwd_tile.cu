@@ -561,13 +561,14 @@ cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float
     default: e = launch_agg<CfgA>(a, s, st, spec); break;
   }
   if (e != cudaSuccess) return e;
-  if (a.gconf_part != nullptr) {
-    const int VC = s.V * s.C;
-    k_conf_reduce_tiles<<<dim3((VC + 31) / 32, s.B), dim3(32, 8), 0, st>>>(a.gconf_part, grad_conf, VC,
-                                                                          a.nt0 * a.nt1 * a.nt2);
-    e = cudaGetLastError();
-  }
+  if (a.gconf_part != nullptr) e = launch_conf_reduce_rows(a.gconf_part, grad_conf, s.B, s.V * s.C, a.nt0 * a.nt1 * a.nt2, st);
   return e;
+}
+
+// grad_conf (B, V*C) = sum of the `nrows` partial rows per item, in row order (shared with the scatter kernel)
+cudaError_t launch_conf_reduce_rows(const float* part, float* grad_conf, int B, int VC, int nrows, cudaStream_t st) {
+  k_conf_reduce_tiles<<<dim3((VC + 31) / 32, B), dim3(32, 8), 0, st>>>(part, grad_conf, VC, nrows);
+  return cudaGetLastError();
 }
 
 }  // namespace lt

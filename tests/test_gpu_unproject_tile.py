@@ -83,6 +83,23 @@ def test_tile_backward_grad_conf_is_deterministic(monkeypatch):
     assert torch.equal(runs[0], runs[1]) and torch.equal(runs[0], runs[2])
 
 
+@pytest.mark.parametrize("shape", [dict(C=32, V=4, N=32), dict(C=40, V=6, N=(8, 8, 16)), dict(C=130, V=2, N=(8, 8, 8))])
+def test_scatter_backward_grad_conf_is_deterministic(shape, monkeypatch):
+    """The default (scatter) kernel as well: warps of a CTA are summed through shared memory in warp order, CTAs and
+    rounds leave one partial row each, rows are summed in row order; no atomics on the grad_conf path. Every
+    lanes-per-voxel instantiation (32 / 64 / 256 padded channels), more than one view chunk."""
+    monkeypatch.setenv("LT_B200_K1BWD", "scatter")
+    d = synthetic.make_unproject_inputs(B=2, H=24, W=24, seed=17, train=True, conf="conf", inside_view=True, **shape)
+    n = shape["N"] if isinstance(shape["N"], tuple) else (shape["N"],) * 3
+    gout = torch.randn((2, shape["C"]) + n, generator=torch.Generator().manual_seed(8)).cuda()
+    runs = [_grads(d, "conf", gout, True)[2] for _ in range(3)]
+    assert torch.equal(runs[0], runs[1]) and torch.equal(runs[0], runs[2])
+    hm_ref = d["heatmaps"].clone().requires_grad_(True)
+    vc_ref = d["vol_confidences"].clone().requires_grad_(True)
+    ref_ops.unproject_heatmaps(hm_ref, d["proj_matricies"], d["coord_volumes"], "conf", vc_ref).backward(gout.cpu())
+    assert rel_err(runs[0].cpu(), vc_ref.grad) < GRAD_TOL
+
+
 def test_degenerate_key_boxes_still_exact(monkeypatch):
     """A camera INSIDE the cuboid makes tile corners fall behind it: the sort keys fall back to the whole image and get
     clamped into the last histogram bin. The order only decides how much merges, never the result."""

@@ -27,7 +27,8 @@ def main():
         m = re.match(r"\s*Function : (\S+)", line)
         if m:
             name = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip() or m.group(1)
-            name = re.sub(r"\(.*", "", name).replace("void ", "").replace("lt::", "").replace("(anonymous namespace)::", "")
+            name = name.replace("(anonymous namespace)::", "").replace("void ", "").replace("lt::", "")
+            name = re.sub(r"\((const |float|UnprojArgs|lt|KArgs|int|unsigned|long|double|void).*", "", name)
             counts[name] = collections.Counter()
             continue
         if name is None or "/*" not in line:
