@@ -106,6 +106,19 @@ int lt_softargmax_fwd(const float *vol, const float *coord, float *coords, float
 /* log-sum-exp merge of R slabs' tuples: parts (R,B*J,5) -> merged (B*J,5); deterministic order. */
 int lt_softargmax_merge(const float *parts, float *merged, int R, int BJ, int softmax, void *stream);
 
+/* lt_softargmax_fwd without caller-owned scratch, for callers that cannot allocate (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernels and bit-identical results as lt_softargmax_fwd; `stats` and `ws` live in one
+ * static device array of LT_NOALLOC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until
+ * exit).  Shapes whose scratch (256-rounded B*J*5*4 + lt_softargmax_ws_bytes(B, J, nvox)) exceeds that maximum are
+ * rejected with LT_ERR_INVALID and a message; 8 MiB covers BASELINE config 3 (16 x 17 joints at 64^3: 6.3 MB)
+ * and one item x 17 joints at 128^3 (3.1 MB), not 256^3 (25 MB for one item).  Calls no cudaMalloc / cudaFree / allocating routine.  Every call shares the array
+ * and finds the last call's contents in it (nothing in it needs clearing between calls): calls that overlap on the
+ * GPU - unordered streams, or two host threads on one device - race; calls ordered on one stream are safe. */
+#define LT_NOALLOC_SCRATCH_BYTES (8u << 20)
+int lt_softargmax_fwd_noalloc(const float *vol, const float *coord, float *coords, float *prob, int B, int J,
+                              long long nvox, int softmax, float multiplier, void *stream);
+
 /* Backward.  grad_coords (B,J,3); grad_prob (B,J,nvox) or NULL (the dense gradient that arrives
  * through the second return value, loss.py:76); prob = saved second output; coords = saved first
  * output (global coordinates, also in the slab-sharded case); grad_vol (B,J,nvox) includes the

@@ -36,6 +36,7 @@ SIGNATURES = {
     "lt_softargmax_finalize": (_i, [_vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f, _vp]),
     "lt_softargmax_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f, _vp]),
     "lt_softargmax_merge": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "lt_softargmax_fwd_noalloc": (_i, [_vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f, _vp]),
     "lt_softargmax_bwd_dot": (_i, [_vp, _vp, _vp, _vp, _i, _i, _ll, _vp]),
     "lt_softargmax_bwd": (_i, [_vp] * 7 + [_i, _i, _ll, _i, _f, _vp]),
     "lt_unproject_fwd_spec": (_i, [_vp, _vp, _vp, _i, _vp, _vp] + [_i] * 10 + [_vp]),

@@ -386,3 +386,76 @@ LT_API int lt_dlt_bwd(const float* grad_out, const float* proj, const float* pts
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// lt_softargmax_fwd_noalloc — K2 forward for callers that cannot allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc). No counterpart in the reference.
+//
+// lt_softargmax_fwd needs two caller-owned scratch buffers (the per-warp tuples `ws` and the merged `stats`); here both
+// live in ONE file-scope device array of LT_NOALLOC_SCRATCH_BYTES that every GPU loading this library holds until exit.
+// `g_noalloc_scratch` below is, in host code, only a stand-in for the symbol: its device address is taken once per
+// device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels receive. The kernels are
+// the ones lt_softargmax_fwd launches (lt::launch_softargmax_fwd), so results are bit-identical to it.
+//
+// Nothing in the scratch must start at zero on the default (split) path: k_sam_stats writes every tuple k_sam_combine
+// reads, k_sam_combine writes every stats row k_sam_final reads; the opt-in fused path (LT_B200_K2FWD=fused) clears its
+// own control words with cudaMemsetAsync on the caller's stream. All calls share the array and find the previous
+// call's contents in it: calls that overlap on the GPU (different streams without an ordering between them, or two host
+// threads on one device) RACE on it. Calls on one stream, or ordered by events, are safe.
+// No cudaMalloc / cudaFree / allocating library routine is called here or below.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[LT_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kNoallocMaxDevices = 64;
+
+// device address of g_noalloc_scratch on the CURRENT device (one cudaGetSymbolAddress per device and process)
+cudaError_t noalloc_scratch(unsigned char** out) {
+  static void* ptrs[kNoallocMaxDevices] = {};  // written once per device; a racing second writer stores the same value
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kNoallocMaxDevices) return cudaErrorInvalidDevice;
+  void* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    if (p == nullptr) return cudaErrorInvalidSymbol;
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = static_cast<unsigned char*>(p);
+  return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" {
+
+LT_API int lt_softargmax_fwd_noalloc(const float* vol, const float* coord, float* coords, float* prob, int B, int J,
+                                     long long nvox, int softmax, float multiplier, void* stream) {
+  LT_REQUIRE(B >= 0 && J >= 0 && nvox >= 0, "negative extent");
+  LT_REQUIRE(B <= 65535 && (long long)B * J <= 65535, "B*J > 65535");
+  LT_REQUIRE(multiplier > 0.f, "multiplier must be > 0 (scale on the caller side otherwise)");
+  if (B * J == 0) return 0;
+  LT_REQUIRE(coords && (nvox == 0 || (vol && coord && prob)), "null pointer");
+  // layout of the static array: [stats (B,J,5) fp32, rounded up to 256 bytes][ws of lt_softargmax_ws_bytes]
+  const size_t stats_bytes = ((size_t)B * J * 5 * sizeof(float) + 255) / 256 * 256;
+  const size_t need = stats_bytes + lt::softargmax_ws_bytes(B, J, nvox);
+  if (need > (size_t)LT_NOALLOC_SCRATCH_BYTES) {
+    snprintf(g_err, sizeof(g_err),
+             "lt_softargmax_fwd_noalloc: B=%d J=%d nvox=%lld needs %zu bytes of scratch, the static array holds "
+             "LT_NOALLOC_SCRATCH_BYTES = %zu; use lt_softargmax_fwd with caller-owned scratch",
+             B, J, nvox, need, (size_t)LT_NOALLOC_SCRATCH_BYTES);
+    return LT_ERR_INVALID;
+  }
+  unsigned char* base = nullptr;
+  cudaError_t e = noalloc_scratch(&base);
+  if (e != cudaSuccess) return finish(__func__, e);
+  float* stats = reinterpret_cast<float*>(base);
+  void* ws = base + stats_bytes;
+  return finish(__func__, lt::launch_softargmax_fwd(vol, coord, coords, nvox == 0 ? nullptr : prob, stats, ws, B, J,
+                                                    nvox, softmax ? 1 : 0, multiplier, as_stream(stream)));
+}
+
+}  // extern "C"
