@@ -40,6 +40,10 @@ cudaError_t launch_conf_reduce_rows(const float* part, float* grad_conf, int B, 
 cudaError_t launch_unproject_bwd_tile(UnprojArgs& a, const UnprojShape& s, float* grad_conf, cudaStream_t st,
                                       const CoordSpecArg* spec);
 
+// persistent TMA-staged formulation of the forward (unproject_fwd_tma.cu): 32-channel features, <= 4 views, N2 % 8 == 0
+bool unproject_fwd_tma_eligible(const UnprojArgs& a);
+cudaError_t launch_unproject_fwd_tma(const UnprojArgs& a, const CoordSpecArg* spec, int agg, cudaStream_t st);
+
 size_t softargmax_ws_bytes(int B, int J, long long nvox);
 cudaError_t launch_softargmax_partial(const float* vol, const float* coord, float* stats, void* ws, int B,
                                       int J, long long nvox, int softmax, float mult, cudaStream_t st,

@@ -256,6 +256,35 @@ struct SpecSmem<true> {
   }
 };
 
+// softmax over <= 4 views of a channel of one voxel: out = sum_v s_v e^{s_v} / sum_v e^{s_v}, two channels per call.
+// Absent views carry kNoView (e -> 0). ex2.approx / rcp.approx are good to ~2 ulp, far inside the 1e-5 bar (round 1
+// started with expf + IEEE divisions at 97 % SFU load, then a 3-comparator sorting network that skipped the
+// exponential of the maximum; this form trades one more MUFU for half the issue slots).
+// Packed forms (FFMA2 / FMUL2 / FADD2) wherever the ISA has one: shift by the maximum of the four views (3 FMNMX per
+// channel), all four exponentials evaluated (the SFU has room: 30 % busy), numerator and denominator accumulated as
+// pairs. ~15 issue slots per channel instead of ~25.
+__device__ __forceinline__ void softmax_mix4_x2(const float (&a)[4], const float (&b)[4], float& out_a, float& out_b) {
+  const float ma = fmaxf(fmaxf(a[0], a[1]), fmaxf(a[2], a[3]));
+  const float mb = fmaxf(fmaxf(b[0], b[1]), fmaxf(b[2], b[3]));
+  const f2 L2 = pack2(kLog2eF, kLog2eF);
+  const f2 nm = mul2(pack2(-ma, -mb), L2);            // -m*log2e per channel
+  f2 num = pack2(0.f, 0.f), den = pack2(0.f, 0.f);
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    const f2 sv = pack2(a[v], b[v]);
+    float ta, tb;
+    unpack2(fma2(sv, L2, nm), ta, tb);               // (s - m)*log2e, <= 0
+    const f2 e = pack2(fast_ex2(ta), fast_ex2(tb));  // absent views (kNoView) underflow to exactly 0
+    den = add2(den, e);
+    num = fma2(sv, e, num);
+  }
+  float na, nb, da, db;
+  unpack2(num, na, nb);
+  unpack2(den, da, db);
+  out_a = na * fast_rcp(da);
+  out_b = nb * fast_rcp(db);
+}
+
 void fill_unproj_tiling(UnprojArgs& a, int lpv);
 int unproj_lpv(int Cp);
 

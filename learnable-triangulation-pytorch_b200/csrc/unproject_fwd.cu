@@ -3,38 +3,11 @@
 // Replaces the B·V python iterations of mvn/utils/op.py:107-161 (project, mask, normalise, F.grid_sample,
 // zero invalid, stack (V,C,N^3), aggregate) with one launch that never materialises per-view volumes.
 // Algorithmic HBM bytes per batch item: F + K + O = V*H*W*Cp*4 + nvox*12 + C*nvox*4.
+#include <stdlib.h>
+
 #include "unproject.cuh"
 
 namespace lt {
-
-// softmax over <= 4 views of a channel of one voxel: out = sum_v s_v e^{s_v} / sum_v e^{s_v}, two channels per call.
-// Absent views carry kNoView (e -> 0). ex2.approx / rcp.approx are good to ~2 ulp, far inside the 1e-5 bar (round 1
-// started with expf + IEEE divisions at 97 % SFU load, then a 3-comparator sorting network that skipped the
-// exponential of the maximum; this form trades one more MUFU for half the issue slots).
-// Packed forms (FFMA2 / FMUL2 / FADD2) wherever the ISA has one: shift by the maximum of the four views (3 FMNMX per
-// channel), all four exponentials evaluated (the SFU has room: 30 % busy), numerator and denominator accumulated as
-// pairs. ~15 issue slots per channel instead of ~25.
-__device__ __forceinline__ void softmax_mix4_x2(const float (&a)[4], const float (&b)[4], float& out_a, float& out_b) {
-  const float ma = fmaxf(fmaxf(a[0], a[1]), fmaxf(a[2], a[3]));
-  const float mb = fmaxf(fmaxf(b[0], b[1]), fmaxf(b[2], b[3]));
-  const f2 L2 = pack2(kLog2eF, kLog2eF);
-  const f2 nm = mul2(pack2(-ma, -mb), L2);            // -m*log2e per channel
-  f2 num = pack2(0.f, 0.f), den = pack2(0.f, 0.f);
-#pragma unroll
-  for (int v = 0; v < 4; ++v) {
-    const f2 sv = pack2(a[v], b[v]);
-    float ta, tb;
-    unpack2(fma2(sv, L2, nm), ta, tb);               // (s - m)*log2e, <= 0
-    const f2 e = pack2(fast_ex2(ta), fast_ex2(tb));  // absent views (kNoView) underflow to exactly 0
-    den = add2(den, e);
-    num = fma2(sv, e, num);
-  }
-  float na, nb, da, db;
-  unpack2(num, na, nb);
-  unpack2(den, da, db);
-  out_a = na * fast_rcp(da);
-  out_b = nb * fast_rcp(db);
-}
 
 // AGG: lt_agg.  ALIGNED: N2 % 8 == 0 so every run is a whole, 32-byte aligned sector.
 // kAggSoftmax is only launched here for V <= kViewChunk (all samples of a voxel in registers); more views go to
@@ -313,6 +286,10 @@ cudaError_t launch_unproject_fwd(const float* feat_hwc, const float* proj, const
   if (s.B == 0 || s.C == 0 || a.nvox == 0) return cudaSuccess;
   const int lpv = unproj_lpv(a.Cp);
   fill_unproj_tiling(a, lpv);
+  // LT_B200_K1FWD=tma: the persistent shared-memory-staged kernel (unproject_fwd_tma.cu) where it applies
+  // (MEASURED at cfg3: 0.76 ms against 0.50 ms for the kernels below, so it is opt-in; read per call so that tests can switch)
+  const char* k1fwd = getenv("LT_B200_K1FWD");
+  if (k1fwd != nullptr && k1fwd[0] == 't' && unproject_fwd_tma_eligible(a)) return launch_unproject_fwd_tma(a, spec, s.agg, st);
   const long long nblk = (long long)a.B * a.ncb * a.nt0 * a.nt1 * a.nt2;
   if (nblk > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
   dim3 grid((unsigned)nblk);
