@@ -26,7 +26,9 @@ inline cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
 
 bool bad_unproj_shape(int B, int V, int C, int H, int W, int N0, int N1, int N2) {
   return B < 0 || V < 1 || C < 0 || H < 1 || W < 1 || N0 < 0 || N1 < 0 || N2 < 0 ||
-         (long long)(H + 2) * (W + 2) * lt::padded_channels(C > 0 ? C : 1) > 0x0fffffffLL;
+         (long long)(H + 2) * (W + 2) * lt::padded_channels(C > 0 ? C : 1) > 0x0fffffffLL ||
+         // tap descriptors are 32-bit float offsets from an item's first map (unproject.cuh build_descs)
+         (long long)V * (H + 2) * (W + 2) * lt::padded_channels(C > 0 ? C : 1) > 0x7fffffffLL;
 }
 
 }  // namespace

@@ -192,6 +192,10 @@ __device__ __forceinline__ void build_descs(const KArgs<SPEC>& a, int b, int i0_
                                             const float4* s_proj, float4 (*s_w)[TileGeom<LPV>::kSlots],
                                             int (*s_off)[TileGeom<LPV>::kSlots], int v0, int nv, int zsel, int lane,
                                             float invH, float invW, const float* s_spec) {
+  // The descriptor offset is relative to the ITEM's first map: view v's maps start v * viewStride floats further on.
+  // (MEASURED with ncu's source view: as `base + (size_t)v * viewStride + off` per tap, 64-bit address arithmetic was
+  // 17-35 instructions per (voxel, view) in the gather loops, half of their instruction count.)
+  const int viewStrideI = (a.H + 2) * (a.W + 2) * a.Cp;
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   const float* coord_b = a.coord + (size_t)b * a.nvox * 3;
@@ -215,6 +219,7 @@ __device__ __forceinline__ void build_descs(const KArgs<SPEC>& a, int b, int i0_
           r0 = __ldg(pp); r1 = __ldg(pp + 1); r2 = __ldg(pp + 2);
         }
         make_desc(x, y, z, r0, r1, r2, a.H, a.W, a.Cp, invH, invW, a.align_corners, off, w);
+        if (off >= 0) off += v * viewStrideI;
       }
       s_w[vv][slot] = w;
       s_off[vv][slot] = off;
@@ -222,15 +227,25 @@ __device__ __forceinline__ void build_descs(const KArgs<SPEC>& a, int b, int i0_
   }
 }
 
-// per-lane gather of one tap set: 4 x LDG.E.128 (4 channels each; the LPV lanes of a voxel read one full texel)
-// and the bilinear blend, accumulated in the nw, ne, sw, se order of ATen's grid_sampler_2d.
-__device__ __forceinline__ void gather4(const float* __restrict__ fv, int off, const float4& w, int Cp,
-                                        int rowStride, float (&s)[kCPL]) {
-  const float* p = fv + off;
+// an opaque copy of a pointer: the compiler keeps it as a 64-bit register pair instead of re-deriving it from the kernel
+// argument plus a 64-bit index at every use (two extra instructions per address in the gather loops)
+template <typename T>
+__device__ __forceinline__ T* opaque_ptr(T* p) {
+  asm volatile("" : "+l"(p));
+  return p;
+}
+
+// the same with both row pointers prepared by the caller (once per CTA): address arithmetic = 2 x (LEA, LEA.HI.X)
+template <int CPT = 0>
+__device__ __forceinline__ void gather4_rows(const float* __restrict__ row0, const float* __restrict__ row1, int off,
+                                             const float4& w, int Cp, float (&s)[kCPL]) {
+  const int cp = CPT > 0 ? CPT : Cp;
+  const float* p = row0 + off;
+  const float* p2 = row1 + off;
   const float4 t00 = ldg128_nc(p);
-  const float4 t01 = ldg128_nc(p + Cp);
-  const float4 t10 = ldg128_nc(p + rowStride);
-  const float4 t11 = ldg128_nc(p + rowStride + Cp);
+  const float4 t01 = ldg128_nc(p + cp);
+  const float4 t10 = ldg128_nc(p2);
+  const float4 t11 = ldg128_nc(p2 + cp);
   // two channels per FFMA2 (the weight operand is broadcast by the instruction): same nw, ne, sw, se chain per channel
   const f2 wx = pack2(w.x, w.x), wy = pack2(w.y, w.y), wz = pack2(w.z, w.z), ww = pack2(w.w, w.w);
   f2 lo = mul2(pack2(t00.x, t00.y), wx), hi = mul2(pack2(t00.z, t00.w), wx);
@@ -239,6 +254,15 @@ __device__ __forceinline__ void gather4(const float* __restrict__ fv, int off, c
   lo = fma2(pack2(t11.x, t11.y), ww, lo); hi = fma2(pack2(t11.z, t11.w), ww, hi);
   unpack2(lo, s[0], s[1]);
   unpack2(hi, s[2], s[3]);
+}
+
+// per-lane gather of one tap set: 4 x LDG.E.128 (4 channels each; the LPV lanes of a voxel read one full texel)
+// and the bilinear blend, accumulated in the nw, ne, sw, se order of ATen's grid_sampler_2d.
+// CPT > 0: the texel pitch is a compile-time constant (an immediate offset of the load instead of a 64-bit add).
+template <int CPT = 0>
+__device__ __forceinline__ void gather4(const float* __restrict__ fv, int off, const float4& w, int Cp,
+                                        int rowStride, float (&s)[kCPL]) {
+  gather4_rows<CPT>(fv, fv + rowStride, off, w, Cp, s);
 }
 
 // shared-memory home of the item's spec: exists only in the SPEC instantiations (a dummy array in the tensor-path

@@ -18,11 +18,12 @@ namespace lt {
 
 
 // scatter-add w_tap * d[0..3] into the four taps; taps with zero weight (outside the map) are skipped.
-__device__ __forceinline__ void scatter4(float* __restrict__ gv, int off, const float4& w, int Cp,
-                                         int rowStride, const float (&d)[kCPL]) {
-  float* p = gv + off;
-  const int dx = Cp;
-  const int dy = rowStride;
+template <int CPT = 0>
+__device__ __forceinline__ void scatter4_rows(float* __restrict__ row0, float* __restrict__ row1, int off, const float4& w,
+                                              int Cp, const float (&d)[kCPL]) {
+  float* p = row0 + off;
+  float* p2 = row1 + off;
+  const int dx = CPT > 0 ? CPT : Cp;
   const f2 dlo = pack2(d[0], d[1]), dhi = pack2(d[2], d[3]);
   float a0, a1, a2, a3;
   if (w.x != 0.f) {
@@ -38,12 +39,12 @@ __device__ __forceinline__ void scatter4(float* __restrict__ gv, int off, const 
   if (w.z != 0.f) {
     const f2 ws = pack2(w.z, w.z);
     unpack2(mul2(dlo, ws), a0, a1); unpack2(mul2(dhi, ws), a2, a3);
-    red_add_v4(p + dy, a0, a1, a2, a3);
+    red_add_v4(p2, a0, a1, a2, a3);
   }
   if (w.w != 0.f) {
     const f2 ws = pack2(w.w, w.w);
     unpack2(mul2(dlo, ws), a0, a1); unpack2(mul2(dhi, ws), a2, a3);
-    red_add_v4(p + dy + dx, a0, a1, a2, a3);
+    red_add_v4(p2 + dx, a0, a1, a2, a3);
   }
 }
 
@@ -52,8 +53,10 @@ struct BwdCtx {
   int warp, lane, g, q, i0_warp, i1_warp, z0, c_lane, rowStride;
   size_t viewStride;
   float invH, invW;
-  const float* fb;
-  float* gb;
+  const float* fb;    // the item's feature maps at this lane's channels; fb1 = one row further down
+  const float* fb1;
+  float* gb;          // the same positions in the gradient map
+  float* gb1;
 };
 
 template <int LPV, bool SPEC>
@@ -71,8 +74,10 @@ __device__ __forceinline__ BwdCtx bwd_prologue(const KArgs<SPEC>& a, const TileI
   c.rowStride = (a.W + 2) * a.Cp;
   c.viewStride = (size_t)(a.H + 2) * (a.W + 2) * a.Cp;
   c.c_lane = T.cb * (LPV * kCPL) + c.q * kCPL;
-  c.fb = a.feat + (size_t)T.b * a.V * c.viewStride + c.c_lane;
-  c.gb = a.gfeat + (size_t)T.b * a.V * c.viewStride + c.c_lane;
+  c.fb = opaque_ptr(a.feat + (size_t)T.b * a.V * c.viewStride + c.c_lane);
+  c.fb1 = opaque_ptr(c.fb + c.rowStride);
+  c.gb = opaque_ptr(a.gfeat + (size_t)T.b * a.V * c.viewStride + c.c_lane);
+  c.gb1 = opaque_ptr(c.gb + c.rowStride);
   return c;
 }
 
@@ -110,6 +115,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
+  constexpr int CPT = LPV < kMaxLanesPerVoxel ? LPV * kCPL : 0;   // texel pitch: Cp == LPV * 4 unless channel-blocked
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float4* s_proj = reinterpret_cast<float4*>(smem_raw);
   auto s_w = reinterpret_cast<float4(*)[kViewChunk][SLOTS]>(s_proj + kMaxViewsSmem * 3);
@@ -165,7 +171,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
                 float d[kCPL];
                 if (AGG == kAggConf) {
                   float s[kCPL];
-                  gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, s);
+                  gather4_rows<CPT>(c.fb, c.fb1, off, w, a.Cp, s);
 #pragma unroll
                   for (int k = 0; k < kCPL; ++k) {
                     gcw[vv][k] = fmaf(go[k], s[k], gcw[vv][k]);
@@ -175,7 +181,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
 #pragma unroll
                   for (int k = 0; k < kCPL; ++k) d[k] = go[k];
                 }
-                scatter4(c.gb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, d);
+                scatter4_rows<CPT>(c.gb, c.gb1, off, w, a.Cp, d);
               }
             }
           }
@@ -192,7 +198,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
             if (vv < nv) {
               offs[vv] = s_off[warp][vv][slot];
               if (offs[vv] >= 0)
-                gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, offs[vv], s_w[warp][vv][slot], a.Cp, c.rowStride, s[vv]);
+                gather4_rows<CPT>(c.fb, c.fb1, offs[vv], s_w[warp][vv][slot], a.Cp, s[vv]);
             }
           }
           float d[kViewChunk][kCPL];
@@ -224,7 +230,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
 #pragma unroll
           for (int vv = 0; vv < kViewChunk; ++vv)
             if (vv < nv && offs[vv] >= 0)
-              scatter4(c.gb + (size_t)(v0 + vv) * c.viewStride, offs[vv], s_w[warp][vv][slot], a.Cp, c.rowStride, d[vv]);
+              scatter4_rows<CPT>(c.gb, c.gb1, offs[vv], s_w[warp][vv][slot], a.Cp, d[vv]);
         }
       }
 
@@ -264,6 +270,7 @@ template <int LPV, int AGG, bool ALIGNED, bool SPEC>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyviews(const KArgs<SPEC> a) {
   using TG = TileGeom<LPV>;
   constexpr int SLOTS = TG::kSlots;
+  constexpr int CPT = LPV < kMaxLanesPerVoxel ? LPV * kCPL : 0;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float4* s_proj = reinterpret_cast<float4*>(smem_raw);
   auto s_w = reinterpret_cast<float4(*)[kViewChunk][SLOTS]>(s_proj + kMaxViewsSmem * 3);
@@ -300,7 +307,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
 #pragma unroll
           for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
           const int off = s_off[warp][vv][g];
-          if (off >= 0) gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, off, s_w[warp][vv][g], a.Cp, c.rowStride, s);
+          if (off >= 0) gather4_rows<CPT>(c.fb, c.fb1, off, s_w[warp][vv][g], a.Cp, s);
 #pragma unroll
           for (int k = 0; k < kCPL; ++k) {
             if (s[k] > m[k]) am[k] = v0 + vv;
@@ -335,7 +342,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
           float d[kCPL];
           if (AGG == kAggSoftmax) {
             float s[kCPL];
-            gather4(c.fb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, s);
+            gather4_rows<CPT>(c.fb, c.fb1, off, w, a.Cp, s);
 #pragma unroll
             for (int k = 0; k < kCPL; ++k) d[k] = gi[k] * fast_ex2((s[k] - m[k]) * kLog2eF) * (o1[k] + s[k]);
           } else {
@@ -347,7 +354,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_bwd_manyview
             }
             if (!any) continue;
           }
-          scatter4(c.gb + (size_t)(v0 + vv) * c.viewStride, off, w, a.Cp, c.rowStride, d);
+          scatter4_rows<CPT>(c.gb, c.gb1, off, w, a.Cp, d);
         }
       }
     }

@@ -20,6 +20,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
+  constexpr int CPT = LPV < kMaxLanesPerVoxel ? LPV * kCPL : 0;   // texel pitch: Cp == LPV * 4 unless channel-blocked
 
   // dynamic smem (> 48 KB): projection rows | tap weights | tap offsets | per-lane result slots (4 ch x 8 z steps)
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -44,7 +45,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
   const int rowStride = (a.W + 2) * a.Cp;
   const size_t viewStride = (size_t)(a.H + 2) * (a.W + 2) * a.Cp;
   const int c_lane = T.cb * (LPV * kCPL) + q * kCPL;  // first channel of this lane
-  const float* fb = a.feat + (size_t)T.b * a.V * viewStride + c_lane;
+  const float* fb = opaque_ptr(a.feat + (size_t)T.b * a.V * viewStride + c_lane);   // the item's maps, this lane's channels
+  const float* fb1 = opaque_ptr(fb + rowStride);                                       // the row below
 
 #pragma unroll 1
   for (int r = 0; r < TG::R; ++r) {
@@ -86,7 +88,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
             if (vv < nv) {
               const int off = s_off[warp][vv][slot];
               if (off >= 0)
-                gather4(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][slot], a.Cp, rowStride, s[vv]);
+                gather4_rows<CPT>(fb, fb1, off, s_w[warp][vv][slot], a.Cp, s[vv]);
             }
           }
 #pragma unroll
@@ -110,7 +112,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1F_CTAS) k_unproject_fw
 #pragma unroll
               for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
               const int off = s_off[warp][vv][slot];
-              if (off >= 0) gather4(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][slot], a.Cp, rowStride, s);
+              if (off >= 0) gather4_rows<CPT>(fb, fb1, off, s_w[warp][vv][slot], a.Cp, s);
 #pragma unroll
               for (int k = 0; k < kCPL; ++k) {
                 if (AGG == kAggSum) val[k] += s[k];
@@ -157,6 +159,7 @@ template <int LPV, bool ALIGNED, bool SPEC>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_manyviews(const KArgs<SPEC> a) {
   using TG = TileGeom<LPV>;
   constexpr int SLOTS = TG::kSlots;
+  constexpr int CPT = LPV < kMaxLanesPerVoxel ? LPV * kCPL : 0;
   __shared__ float4 s_proj[kMaxViewsSmem * 3];
   __shared__ float4 s_w[kWarpsPerCta][kViewChunk][SLOTS];
   __shared__ int s_off[kWarpsPerCta][kViewChunk][SLOTS];
@@ -176,7 +179,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
   const int rowStride = (a.W + 2) * a.Cp;
   const size_t viewStride = (size_t)(a.H + 2) * (a.W + 2) * a.Cp;
   const int c_lane = T.cb * (LPV * kCPL) + q * kCPL;
-  const float* fb = a.feat + (size_t)T.b * a.V * viewStride + c_lane;
+  const float* fb = opaque_ptr(a.feat + (size_t)T.b * a.V * viewStride + c_lane);   // the item's maps, this lane's channels
+  const float* fb1 = opaque_ptr(fb + rowStride);                                       // the row below
 
 #pragma unroll 1
   for (int r = 0; r < TG::R; ++r) {
@@ -199,7 +203,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 2) k_unproject_fwd_softmax_
 #pragma unroll
           for (int k = 0; k < kCPL; ++k) s[k] = 0.f;
           const int off = s_off[warp][vv][g];
-          if (off >= 0) gather4(fb + (size_t)(v0 + vv) * viewStride, off, s_w[warp][vv][g], a.Cp, rowStride, s);
+          if (off >= 0) gather4_rows<CPT>(fb, fb1, off, s_w[warp][vv][g], a.Cp, s);
 #pragma unroll
           for (int k = 0; k < kCPL; ++k) {
             const float mn = fmaxf(m[k], s[k]);
