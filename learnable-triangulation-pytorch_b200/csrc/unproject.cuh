@@ -256,6 +256,36 @@ __device__ __forceinline__ void gather4_rows(const float* __restrict__ row0, con
   unpack2(hi, s[2], s[3]);
 }
 
+// The two halves of gather4_rows for callers that want the loads of SEVERAL views in flight before the first blend
+// (a branch per view serialises them: one L2 round trip per view instead of one per voxel). The loads are predicated on
+// off >= 0 and leave t undefined otherwise; blend_taps then returns exactly 0 for that view.
+template <int CPT = 0>
+__device__ __forceinline__ void issue_taps(const float* __restrict__ row0, const float* __restrict__ row1, int off, int Cp,
+                                           float4 (&t)[4]) {
+  const int cp = CPT > 0 ? CPT : Cp;
+  const float* p = row0 + off;
+  const float* p2 = row1 + off;
+#define LT_LDG_IF(dst, ptr)                                                                                         \
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %5, 0;\n\t@p ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];\n\t}"    \
+               : "=f"(dst.x), "=f"(dst.y), "=f"(dst.z), "=f"(dst.w) : "l"(ptr), "r"(off))
+  LT_LDG_IF(t[0], p);
+  LT_LDG_IF(t[1], p + cp);
+  LT_LDG_IF(t[2], p2);
+  LT_LDG_IF(t[3], p2 + cp);
+#undef LT_LDG_IF
+}
+__device__ __forceinline__ void blend_taps(const float4 (&t)[4], const float4& w, int off, float (&s)[kCPL]) {
+  const f2 wx = pack2(w.x, w.x), wy = pack2(w.y, w.y), wz = pack2(w.z, w.z), ww = pack2(w.w, w.w);
+  f2 lo = mul2(pack2(t[0].x, t[0].y), wx), hi = mul2(pack2(t[0].z, t[0].w), wx);
+  lo = fma2(pack2(t[1].x, t[1].y), wy, lo); hi = fma2(pack2(t[1].z, t[1].w), wy, hi);
+  lo = fma2(pack2(t[2].x, t[2].y), wz, lo); hi = fma2(pack2(t[2].z, t[2].w), wz, hi);
+  lo = fma2(pack2(t[3].x, t[3].y), ww, lo); hi = fma2(pack2(t[3].z, t[3].w), ww, hi);
+  unpack2(lo, s[0], s[1]);
+  unpack2(hi, s[2], s[3]);
+#pragma unroll
+  for (int k = 0; k < kCPL; ++k) s[k] = off >= 0 ? s[k] : 0.f;
+}
+
 // per-lane gather of one tap set: 4 x LDG.E.128 (4 channels each; the LPV lanes of a voxel read one full texel)
 // and the bilinear blend, accumulated in the nw, ne, sw, se order of ATen's grid_sampler_2d.
 // CPT > 0: the texel pitch is a compile-time constant (an immediate offset of the load instead of a 64-bit add).

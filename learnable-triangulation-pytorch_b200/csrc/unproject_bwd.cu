@@ -110,8 +110,14 @@ __device__ __forceinline__ void stage_grad_out(const UnprojArgs& a, int b, int c
 }
 
 // sum / conf for any V; softmax / max for V <= kViewChunk (all samples of a voxel live in registers).
+#ifndef LT_K1B_BATCH
+#define LT_K1B_BATCH 0   // softmax / max: views whose tap loads are in flight together (0 = one branch per view)
+#endif
+#ifndef LT_K1B_CTAS
+#define LT_K1B_CTAS 3
+#endif
 template <int LPV, int AGG, bool ALIGNED, bool SPEC>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KArgs<SPEC> a) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, LT_K1B_CTAS) k_unproject_bwd(const KArgs<SPEC> a) {
   using TG = TileGeom<LPV>;
   constexpr int G = TG::G;
   constexpr int SLOTS = TG::kSlots;
@@ -189,6 +195,32 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
           // softmax / max over <= kViewChunk views, all samples in registers
           float s[kViewChunk][kCPL];
           int offs[kViewChunk];
+#if LT_K1B_BATCH
+          // The tap loads of LT_K1B_BATCH views are issued before the first blend. ncu's source view says that with a
+          // branch per view 48 % of the stall samples are long-scoreboard waits at the first blend of each view, but
+          // MEASURED at cfg3: 2 views / 2 CTAs per SM 1.220 ms, 4 views / 2 CTAs 1.164 ms, 2 views / 3 CTAs (100 bytes of
+          // spills) 1.123 ms, against 1.036 ms for one branch per view at 3 CTAs: the registers the loads in flight need
+          // cost more occupancy (or spills) than the overlap returns. Off by default.
+#pragma unroll
+          for (int vv = 0; vv < kViewChunk; ++vv) offs[vv] = (vv < nv) ? s_off[warp][vv][slot] : -1;
+#pragma unroll
+          for (int vg = 0; vg < kViewChunk; vg += LT_K1B_BATCH) {
+            float4 t[LT_K1B_BATCH][4];
+#pragma unroll
+            for (int u = 0; u < LT_K1B_BATCH; ++u)
+              if (vg + u < nv) issue_taps<CPT>(c.fb, c.fb1, offs[vg + u], a.Cp, t[u]);
+#pragma unroll
+            for (int u = 0; u < LT_K1B_BATCH; ++u) {
+              const int vv = vg + u;
+              if (vv < nv) {
+                blend_taps(t[u], s_w[warp][vv][slot], offs[vv], s[vv]);
+              } else {
+#pragma unroll
+                for (int k = 0; k < kCPL; ++k) s[vv][k] = kNoView;
+              }
+            }
+          }
+#else
 #pragma unroll
           for (int vv = 0; vv < kViewChunk; ++vv) {
             const float fill = (vv < nv) ? 0.f : kNoView;
@@ -201,6 +233,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 3) k_unproject_bwd(const KA
                 gather4_rows<CPT>(c.fb, c.fb1, offs[vv], s_w[warp][vv][slot], a.Cp, s[vv]);
             }
           }
+#endif
           float d[kViewChunk][kCPL];
 #pragma unroll
           for (int k = 0; k < kCPL; ++k) {
