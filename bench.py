@@ -565,12 +565,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--agg", default=None, choices=["sum", "conf", "max", "softmax"],
+                    help="A/B runs only: another view aggregation on the workload's shape (named in config.aggregation)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded CPU sample (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer arm (profiling runs)")
     ap.add_argument("--no-graph", action="store_true", help="e2e arm: launch the python ops eagerly instead of replaying "
                                                             "a CUDA graph captured from them")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
+    if args.agg is not None and args.agg != w["agg"]:
+        w["agg"] = args.agg
+        w["desc"] += " [A/B run: aggregation overridden to %s]" % args.agg
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

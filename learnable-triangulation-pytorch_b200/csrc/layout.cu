@@ -18,34 +18,35 @@
 
 namespace lt {
 
-constexpr int kPixTile = 64;   // pixels (of one padded row) per CTA
+constexpr int kPixTile = 64;   // consecutive padded pixels per CTA
 constexpr int kChanTile = 32;  // channels per CTA (Cp is a multiple of 32)
 
-// one CTA = (64 padded pixels of padded row yp, bv, 32-channel block). smem tile [32][65]: the planar side moves 64
-// consecutive pixels per channel (256-byte runs), the channels-last side 32 consecutive floats per pixel (128 bytes).
+// one CTA = (64 CONSECUTIVE padded pixels of one map in row-major order, bv, 32-channel block): a tile may straddle a row
+// boundary, so every tile but the last of a map is full (per-row chunks left the second chunk of a 98-pixel row 47 %
+// empty). smem tile [32][65]: the planar side moves runs of consecutive pixels per channel, the channels-last side 32
+// consecutive floats per pixel (128 bytes).
 template <bool TO_HWCP>
 __global__ void __launch_bounds__(256) k_feat_layout(const float* __restrict__ src, float* __restrict__ dst, int C,
-                                                     int Cp, int H, int W, int nchunk) {
+                                                     int Cp, int H, int W) {
   __shared__ float tile[kChanTile * (kPixTile + 1)];
   const int Hp = H + 2, Wp = W + 2;
-  const int chunk = blockIdx.x % nchunk, yp = blockIdx.x / nchunk;
   const int bv = blockIdx.y, c0 = blockIdx.z * kChanTile;
-  const int xp0 = chunk * kPixTile;
-  const int npix = min(kPixTile, Wp - xp0);
-  const int y = yp - 1;
-  const bool row_in = (y >= 0 && y < H);
-  const size_t planar_base = ((size_t)bv * C + c0) * H * W + (size_t)(row_in ? y : 0) * W;
-  const size_t hwcp_base = (((size_t)bv * Hp + yp) * Wp + xp0) * Cp + c0;
+  const int P0 = blockIdx.x * kPixTile;
+  const int npix = min(kPixTile, Hp * Wp - P0);
+  const size_t hwcp_base = ((size_t)bv * Hp * Wp + P0) * Cp + c0;
 
-  // planar side: thread -> pixel t%64, channels t/64 + 4k (coalesced 256-byte rows, no index arithmetic in the loop)
+  // planar side: thread -> pixel t%64, channels t/64 + 4k (no index arithmetic in the loop)
   // hwcp side  : thread -> channel quad t%8, pixels t/8 + 32k (one 16-byte vector per thread, 128 bytes per pixel)
   // tile[c*65 + p]: both access patterns are bank-conflict free (65 = 1 mod 32).
   const int pp = threadIdx.x & (kPixTile - 1), pc = threadIdx.x >> 6;
   const int hq = threadIdx.x & 7, hp = threadIdx.x >> 3;
-  const int x = xp0 + pp - 1;
-  const bool px_in = row_in && pp < npix && x >= 0 && x < W;
+  const int P = P0 + pp;
+  const int yp = P / Wp, xp = P - yp * Wp;
+  const int y = yp - 1, x = xp - 1;
+  const bool px_in = pp < npix && y >= 0 && y < H && x >= 0 && x < W;
+  const size_t planar = ((size_t)bv * C + c0 + pc) * H * W + (size_t)(px_in ? y : 0) * W + (px_in ? x : 0);
   if (TO_HWCP) {
-    const float* sp = src + planar_base + (size_t)pc * H * W + x;
+    const float* sp = src + planar;
 #pragma unroll
     for (int k = 0; k < kChanTile / 4; ++k) {
       const int c = pc + 4 * k;
@@ -64,7 +65,6 @@ __global__ void __launch_bounds__(256) k_feat_layout(const float* __restrict__ s
       }
     }
   } else {
-    if (!row_in) return;
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
       const int p = hp + 32 * k;
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256) k_feat_layout(const float* __restrict__ s
       }
     }
     __syncthreads();
-    float* dp = dst + planar_base + (size_t)pc * H * W + x;
+    float* dp = dst + planar;
 #pragma unroll
     for (int k = 0; k < kChanTile / 4; ++k) {
       const int c = pc + 4 * k;
@@ -100,12 +100,12 @@ cudaError_t launch_feat_layout(const float* src, float* dst, int BV, int C, int 
                                cudaStream_t st) {
   if (BV == 0 || C == 0 || H * W == 0) return cudaSuccess;
   const int Cp = padded_channels(C);
-  const int nchunk = (W + 2 + kPixTile - 1) / kPixTile;
-  dim3 grid((unsigned)(nchunk * (H + 2)), (unsigned)BV, (unsigned)(Cp / kChanTile));
+  const int ntile = ((H + 2) * (W + 2) + kPixTile - 1) / kPixTile;
+  dim3 grid((unsigned)ntile, (unsigned)BV, (unsigned)(Cp / kChanTile));
   if (to_hwcp)
-    k_feat_layout<true><<<grid, 256, 0, st>>>(src, dst, C, Cp, H, W, nchunk);
+    k_feat_layout<true><<<grid, 256, 0, st>>>(src, dst, C, Cp, H, W);
   else
-    k_feat_layout<false><<<grid, 256, 0, st>>>(src, dst, C, Cp, H, W, nchunk);
+    k_feat_layout<false><<<grid, 256, 0, st>>>(src, dst, C, Cp, H, W);
   return cudaGetLastError();
 }
 
