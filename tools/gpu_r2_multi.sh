@@ -12,7 +12,7 @@ python - <<PY
 import json
 for w in ("cfg3","cfg5"):
     try:
-        d=json.load(open("gpurun_out/r2m_bench_%s_x$N.json"%w))
+        d=json.loads(open("gpurun_out/r2m_bench_%s_x$N.json"%w).read().strip().splitlines()[-1])
         print(w, "value", round(d["value"]), "e2e", round(d["e2e"]["value"]) if d.get("e2e") else None, d["config"]["parallelism"][:60])
         print("   sharded:", json.dumps(d["roofline"].get("next_rows",{}).get("cfg5_sharded_softargmax"))[:600])
     except Exception as e: print(w, "failed", e)
