@@ -109,7 +109,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-// bounded wait: a protocol error becomes a trap after 4 s instead of a hung GPU
+// bounded wait: a protocol error becomes a trap after 20 s (time-based, as in pwconv.cu) instead of a hung GPU
 __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity) {
   unsigned long long t0 = 0;
   for (unsigned i = 0;; ++i) {
@@ -120,7 +120,7 @@ __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity) {
     if (i >= (1u << 14)) {
       if (t0 == 0) t0 = globaltimer_ns();
       __nanosleep(128);
-      if ((i & 0x3ffu) == 0 && globaltimer_ns() - t0 > 4000000000ull) __trap();
+      if ((i & 0x3ffu) == 0 && globaltimer_ns() - t0 > 20000000000ull) __trap();
     }
   }
 }
