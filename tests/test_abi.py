@@ -51,6 +51,11 @@ def test_host_side_entry_points_without_gpu():
     assert rc == -1 and b"aggregation" in L.lt_last_error()
     with pytest.raises(RuntimeError):
         _lib.check(rc)
+    # tap descriptors are 32-bit offsets from an item's first map: V * (H+2) * (W+2) * Cp must stay below 2^31
+    rc = L.lt_unproject_fwd(None, None, None, None, None, 1, 64, 32, 1022, 1022, 8, 8, 8, 0, 0, None)
+    assert rc == -1 and b"bad shape" in L.lt_last_error()
+    rc = L.lt_unproject_bwd(None, None, None, None, None, None, None, None, 1, 64, 32, 1022, 1022, 8, 8, 8, 0, 0, None)
+    assert rc == -1 and b"bad shape" in L.lt_last_error()
 
 
 def test_missing_library_fails_loudly(monkeypatch):
