@@ -54,6 +54,11 @@ cudaError_t launch_softargmax_finalize(const float* vol, const float* stats, flo
 cudaError_t launch_softargmax_fwd(const float* vol, const float* coord, float* coords, float* prob, float* stats,
                                   void* ws, int B, int J, long long nvox, int softmax, float mult, cudaStream_t st,
                                   const CoordSpecArg* spec = nullptr);
+// one-read forward: a thread-block cluster keeps one (b, joint) volume in shared memory (softargmax_cluster.cu)
+int softargmax_cluster_size(long long nvox);   // 0 = does not apply
+cudaError_t launch_softargmax_fwd_cluster(const float* vol, const float* coord, float* coords, float* prob, float* stats,
+                                          int B, int J, long long nvox, int softmax, float mult, cudaStream_t st,
+                                          const CoordSpecArg* spec);
 cudaError_t launch_softargmax_merge(const float* parts, float* merged, int R, int BJ, int softmax,
                                     cudaStream_t st);
 cudaError_t launch_softargmax_bwd_dot(const float* prob, const float* grad_prob, float* dots, void* ws,

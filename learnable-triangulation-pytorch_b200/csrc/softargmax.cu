@@ -608,7 +608,12 @@ cudaError_t launch_softargmax_fwd(const float* vol, const float* coord, float* c
   // MEASURED at cfg3 (gpurun_out r2e): the fused launch runs 0.289 ms against 0.165 ms for the three launches (the merge
   // of an item's tuples by its last CTA sits on the critical path of a two-item-deep pipeline), so it is opt-in:
   // LT_B200_K2FWD=fused.
-  static const bool split = [] { const char* e = getenv("LT_B200_K2FWD"); return !(e != nullptr && e[0] == 'f'); }();
+  // LT_B200_K2FWD = cluster | fused | (unset: the three launches); read per call so that tests can switch
+  const char* mode = getenv("LT_B200_K2FWD");
+  const bool split = !(mode != nullptr && mode[0] == 'f');
+  if (mode != nullptr && mode[0] == 'c' && B * J > 0 && prob != nullptr && coords != nullptr && stats != nullptr &&
+      softargmax_cluster_size(nvox) > 0 && al16(vol) && al16(prob) && (spec != nullptr || al16(coord)))
+    return launch_softargmax_fwd_cluster(vol, coord, coords, prob, stats, B, J, nvox, softmax, mult, st, spec);
   if (split || B * J == 0 || nvox == 0 || prob == nullptr || coords == nullptr) {
     cudaError_t e = launch_softargmax_partial(vol, coord, stats, ws, B, J, nvox, softmax, mult, st, spec);
     if (e != cudaSuccess) return e;
