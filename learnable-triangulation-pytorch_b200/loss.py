@@ -8,6 +8,7 @@ import torch
 from torch import nn
 
 from . import _lib
+from ._nvtx import annotate
 from .op import _f32c, _require_cuda, _stream
 
 
@@ -47,6 +48,7 @@ class _VolumetricCE(torch.autograd.Function):
         return None, gvol.to(dtype), None, None
 
 
+@annotate("lt_b200.volumetric_ce_loss")
 def volumetric_ce_loss(coord_volumes_batch, volumes_batch_pred, keypoints_gt, keypoints_binary_validity):
     """``-log(p + 1e-6)`` of the predicted volume at the voxel nearest to each ground-truth joint, weighted by the
     joint's validity and averaged over ALL B*J joints (reference: loss.py:56-80).
@@ -151,6 +153,7 @@ class _SoftArgmaxWithCE(torch.autograd.Function):
         return gvol.to(dtype), None, None, None, None, None
 
 
+@annotate("lt_b200.integrate_tensor_3d_with_coordinates_and_ce")
 def integrate_tensor_3d_with_coordinates_and_ce(volumes, coord_volumes, keypoints_gt, keypoints_binary_validity,
                                                 softmax=True, *, multiplier=1.0):
     """``integrate_tensor_3d_with_coordinates`` (op.py:84-96) and ``VolumetricCELoss`` (loss.py:52-80) of its second

@@ -10,6 +10,7 @@ B*J python iterations with one ``torch.svd`` each.
 import torch
 
 from . import _lib
+from ._nvtx import annotate
 from .op import _require_cuda, _f32c, _stream
 
 MAX_VIEWS = 64  # LT_DLT_MAX_VIEWS
@@ -53,6 +54,7 @@ class _DLT(torch.autograd.Function):
         return None, (gpts.to(pts_dtype) if need_pts else None), (gconf.to(conf_dtype) if need_conf else None)
 
 
+@annotate("lt_b200.triangulate_batch_of_points")
 def triangulate_batch_of_points(proj_matricies_batch, points_batch, confidences_batch=None):
     """Confidence-weighted DLT of every (batch item, joint) (reference: multiview.py:162-174).
 

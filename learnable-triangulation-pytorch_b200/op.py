@@ -14,6 +14,7 @@ Everything runs in hand-written sm_100a kernels behind the C ABI of ``include/lt
 import torch
 
 from . import _lib
+from ._nvtx import annotate
 from .coordspec import CoordSpec
 
 _AGG = {"sum": 0, "max": 2, "softmax": 3}  # 'conf*' -> 1, see _agg_code
@@ -170,6 +171,7 @@ class _Unproject(torch.autograd.Function):
         return g_hm, None, None, g_conf, None, None
 
 
+@annotate("lt_b200.unproject_heatmaps")
 def unproject_heatmaps(heatmaps, proj_matricies, coord_volumes, volume_aggregation_method='sum',
                        vol_confidences=None, *, align_corners=None):
     """Lift V feature maps per batch item into one aggregated 3-D volume (reference: op.py:99-163).
@@ -283,6 +285,7 @@ class _SoftArgmax(torch.autograd.Function):
         return gvol.to(dtype), None, None, None
 
 
+@annotate("lt_b200.integrate_tensor_3d_with_coordinates")
 def integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True, *, multiplier=1.0):
     """Soft-argmax of each joint volume in world coordinates (reference: op.py:84-96).
 
@@ -316,6 +319,7 @@ def integrate_tensor_3d_with_coordinates(volumes, coord_volumes, softmax=True, *
     return _SoftArgmax.apply(volumes, coord_volumes, 1 if softmax else 0, multiplier)
 
 
+@annotate("lt_b200.integrate_tensor_3d")
 def integrate_tensor_3d(volumes, softmax=True):
     """Soft-argmax of each joint volume in VOXEL-INDEX coordinates (reference: op.py:50-81; not used by the reference's
     nets, kept so that every ``integrate_*`` of ``mvn.utils.op`` has its counterpart here).
@@ -376,6 +380,7 @@ class _SoftArgmax2D(torch.autograd.Function):
         return ghm.to(dtype), None, None
 
 
+@annotate("lt_b200.integrate_tensor_2d")
 def integrate_tensor_2d(heatmaps, softmax=True, *, multiplier=1.0):
     """Soft-argmax of joint heat maps in heat-map pixels (reference: op.py:11-47).
 

@@ -21,6 +21,7 @@ import torch
 from torch import nn
 
 from . import _lib
+from ._nvtx import annotate
 from . import op as _op
 
 
@@ -79,6 +80,7 @@ class _ProcessFeatures(torch.autograd.Function):
         return gx, gw, gb
 
 
+@annotate("lt_b200.process_features")
 def process_features(features, weight, bias=None):
     """``F.conv2d(features, weight, bias)`` for a 1x1 kernel (the ``process_features`` step, triangulation.py:238-240,
     344-346), written straight into the layout ``op.unproject_heatmaps`` gathers from.

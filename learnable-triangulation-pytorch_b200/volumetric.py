@@ -10,6 +10,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from ._nvtx import annotate
 from .op import _stream
 
 from .coordspec import COORD_SPEC, CoordSpec  # noqa: F401
@@ -46,6 +47,7 @@ def coord_volume_specs(base_points, cuboid_side, volume_size, thetas=None, axis=
     return torch.from_numpy(spec)
 
 
+@annotate("lt_b200.coord_volumes_from_specs")
 def coord_volumes_from_specs(specs, volume_size, transfer_cmu_to_human36m=False):
     """The launch on its own: ``specs`` (B,18) fp32 ALREADY ON THE DEVICE (``coord_volume_specs`` + a pinned,
     non-blocking copy in a data-loading pipeline) -> (B,N0,N1,N2,3). No host work, no synchronisation."""
@@ -64,6 +66,7 @@ def coord_volumes_from_specs(specs, volume_size, transfer_cmu_to_human36m=False)
     return out
 
 
+@annotate("lt_b200.build_coord_volumes")
 def build_coord_volumes(base_points, cuboid_side, volume_size, thetas=None, axis=(0, 0, 1),
                         transfer_cmu_to_human36m=False, device="cuda"):
     """(B, N0, N1, N2, 3) fp32 world coordinates of the voxel centres.

@@ -218,3 +218,29 @@ def test_reference_net_forward_reaches_the_drop_ins_at_its_own_call_sites():
             lt_b200.unpatch_reference()
     finally:
         sys.path.remove("/root/reference")
+
+
+def test_nvtx_ranges_are_opt_in(monkeypatch):
+    """LT_B200_NVTX=1 wraps the public ops in `lt_b200.<op>` ranges; without it the decorator returns the function itself
+    (no wrapper frame on the hot path)."""
+    import importlib
+    from lt_b200 import _nvtx
+    calls = []
+
+    def f(x):
+        return x + 1
+    monkeypatch.setattr(_nvtx, "ENABLED", False)
+    assert _nvtx.annotate("lt_b200.f")(f) is f
+    monkeypatch.setattr(_nvtx, "ENABLED", True)
+    monkeypatch.setattr(torch.cuda.nvtx, "range_push", lambda name: calls.append(("push", name)))
+    monkeypatch.setattr(torch.cuda.nvtx, "range_pop", lambda: calls.append(("pop",)))
+    g = _nvtx.annotate("lt_b200.f")(f)
+    assert g is not f and g(1) == 2 and g.__name__ == "f"
+    assert calls == [("push", "lt_b200.f"), ("pop",)]
+    with pytest.raises(ZeroDivisionError):            # the range is closed when the op raises
+        _nvtx.annotate("lt_b200.h")(lambda: 1 / 0)()
+    assert calls[-2:] == [("push", "lt_b200.h"), ("pop",)]
+    # the public ops carry the decorator (identity by default)
+    import lt_b200
+    assert lt_b200.unproject_heatmaps.__name__ == "unproject_heatmaps"
+    importlib.reload(_nvtx)
