@@ -157,6 +157,7 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const K
   const float invH = 1.f / (float)a.H, invW = 1.f / (float)a.W;
   const int rowStride = (a.W + 2) * kCp;
   const size_t viewStride = (size_t)(a.H + 2) * (a.W + 2) * kCp;
+  const int viewStrideI = (a.H + 2) * (a.W + 2) * kCp;
   const int c_lane = q * kCPL;
   const float* fb = a.feat + (size_t)b * a.V * viewStride + c_lane;
   float* gb = a.gfeat + (size_t)b * a.V * viewStride + c_lane;
@@ -263,7 +264,9 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const K
         const int vv = it / TV, kr = s_kr[it];
         const int pos = (vv == 0 ? 0 : (vv == 1 ? b1 : (vv == 2 ? b2 : b3))) +
                         s_hist[vv * CF::HS + CF::hslot(kr & 0xffff)] + (kr >> 16);
-        s_rec_m[pos] = make_int2(off | vv, it);  // off is a multiple of Cp = 32: the low bits are free
+        // offset relative to the chunk's first map (view stride folded in: one 32-bit index per tap, see build_descs);
+        // a multiple of Cp = 32, so the low bits are free for the view
+        s_rec_m[pos] = make_int2((off + vv * viewStrideI) | vv, it);
         s_rec_w[pos] = s_w[it];
       }
     }
@@ -271,8 +274,10 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const K
     const int chunk = (n_total + NG - 1) / NG;
     const int gid = warp * kG + g;
     const int rec_begin = min(n_total, gid * chunk), rec_end = min(n_total, rec_begin + chunk);
-    const float* fbv = fb + (size_t)v0 * viewStride;
-    float* gbv = gb + (size_t)v0 * viewStride;
+    const float* fbv = opaque_ptr(fb + (size_t)v0 * viewStride);   // opaque 64-bit pairs: see unproject.cuh
+    const float* fbv1 = opaque_ptr(fbv + rowStride);
+    float* gbv = opaque_ptr(gb + (size_t)v0 * viewStride);
+    float* gbv1 = opaque_ptr(gbv + rowStride);
 
     // ---------------- G: samples, gathered in CELL-SORTED order: consecutive records read the same or neighbouring
     // texels, so all but the first touch of a texel hit L1 ----------------
@@ -282,15 +287,15 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const K
       for (; rec + 1 < rec_end; rec += 2) {
         const int2 ma = s_rec_m[rec], mb = s_rec_m[rec + 1];
         float sa[kCPL], sb[kCPL];
-        gather4(fbv + (size_t)(ma.x & 3) * viewStride, ma.x & ~3, s_rec_w[rec], kCp, rowStride, sa);
-        gather4(fbv + (size_t)(mb.x & 3) * viewStride, mb.x & ~3, s_rec_w[rec + 1], kCp, rowStride, sb);
+        gather4_rows<kCp>(fbv, fbv1, ma.x & ~3, s_rec_w[rec], kCp, sa);
+        gather4_rows<kCp>(fbv, fbv1, mb.x & ~3, s_rec_w[rec + 1], kCp, sb);
         s_stage[ma.y * kLPV + q] = make_float4(sa[0], sa[1], sa[2], sa[3]);
         s_stage[mb.y * kLPV + q] = make_float4(sb[0], sb[1], sb[2], sb[3]);
       }
       if (rec < rec_end) {
         const int2 ma = s_rec_m[rec];
         float sa[kCPL];
-        gather4(fbv + (size_t)(ma.x & 3) * viewStride, ma.x & ~3, s_rec_w[rec], kCp, rowStride, sa);
+        gather4_rows<kCp>(fbv, fbv1, ma.x & ~3, s_rec_w[rec], kCp, sa);
         s_stage[ma.y * kLPV + q] = make_float4(sa[0], sa[1], sa[2], sa[3]);
       }
       __syncthreads();
@@ -397,7 +402,8 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const K
     {
       float4 a00 = make_float4(0.f, 0.f, 0.f, 0.f), a01 = a00, a10 = a00, a11 = a00;
       int cur = -64;      // (offset | view) of the cell in the registers; -64 = none (never one cell left of anything)
-      float* pc = gbv;    // its north-west texel in the gradient map
+      float* pc = gbv;    // its north-west texel in the gradient map, and the texel below
+      float* pc1 = gbv1;
 #pragma unroll 1
       for (int rec = rec_begin; rec < rec_end; ++rec) {
         const int2 m = s_rec_m[rec];
@@ -407,10 +413,10 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const K
           const bool shift = (m.x == cur + kCp);  // same view (low bits), next cell to the right in the same row
           if (cur >= 0) {
             red4(pc, a00);
-            red4(pc + rowStride, a10);
+            red4(pc1, a10);
             if (!shift) {
               red4(pc + kCp, a01);
-              red4(pc + rowStride + kCp, a11);
+              red4(pc1 + kCp, a11);
             }
           }
           if (shift) {
@@ -420,15 +426,16 @@ __global__ void __launch_bounds__(CF::NT, CF::CTAS) k_unproject_bwd_tile(const K
           }
           a01 = make_float4(0.f, 0.f, 0.f, 0.f); a11 = a01;
           cur = m.x;
-          pc = gbv + (size_t)(m.x & 3) * viewStride + (m.x & ~3);
+          pc = gbv + (m.x & ~3);
+          pc1 = gbv1 + (m.x & ~3);
         }
         fma4(a00, w.x, d); fma4(a01, w.y, d); fma4(a10, w.z, d); fma4(a11, w.w, d);
       }
       if (cur >= 0) {
         red4(pc, a00);
         red4(pc + kCp, a01);
-        red4(pc + rowStride, a10);
-        red4(pc + rowStride + kCp, a11);
+        red4(pc1, a10);
+        red4(pc1 + kCp, a11);
       }
     }
 
